@@ -1,0 +1,10 @@
+"""B200-native path-tracing backend for the hot path of zhouhang95/ray_tracing_in_one_weekend.
+
+Product = csrc/ (CUDA kernels + C ABI + host scene API) behind include/rtgpu.h; this package is the
+thin ctypes mirror used by tests and bench.py.  No CPU fallback exists.
+"""
+from .api import (  # noqa: F401
+    HostScene, Scene, RtError, RtRenderParams, RtStats, RtFlatScene, RtCamera, HIT_DTYPE, load_library,
+    camera_get_rays, pixel_center_uv, flat_to_numpy, measure_fp32_peak, LIB_PATH, ASSET_DIR, EXPORTED_SYMBOLS,
+    MODE_AUTO, MODE_MEGAKERNEL, MODE_WAVEFRONT, RENDER_COUNTERS,
+)

@@ -1,0 +1,339 @@
+"""ctypes binding of librtgpu.so (include/rtgpu.h) — the only way Python reaches the backend.
+
+There is deliberately no fallback: if the CUDA library is missing or no CUDA device is usable,
+calls raise `RtError`.  The oracle under oracle/ is test infrastructure and is never imported here.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REPO = os.path.dirname(HERE)
+LIB_PATH = os.path.join(HERE, "librtgpu.so")
+ASSET_DIR = os.path.join(REPO, "assets")
+
+RT_ABI_VERSION = 1
+
+# RtPrimKind
+PRIM_SPHERE, PRIM_XYRECT, PRIM_XZRECT, PRIM_YZRECT, PRIM_MOVING_SPHERE, PRIM_MEDIUM = range(6)
+PRIM_FLAG_BOUNDARY_ONLY = 1
+XF_TRANSLATE, XF_ROTATE_Y = 0, 1
+(MAT_EMISSION, MAT_DIFFUSE, MAT_LAMBERT, MAT_METAL, MAT_DIELECTRIC, MAT_ISOTROPIC, MAT_OREN_NAYAR, MAT_BURLEY_DIFFUSE,
+ MAT_ROUGH_PLASTIC, MAT_DISNEY_DIFFUSE, MAT_DISNEY_METAL, MAT_DISNEY_SHEEN, MAT_DISNEY_CLEARCOAT) = range(13)
+TEX_CONSTANT, TEX_CHECKER, TEX_PERLIN, TEX_IMAGE = range(4)
+SKY_GRADIENT, SKY_BLACK, SKY_ENVMAP, SKY_CONSTANT = range(4)
+MODE_AUTO, MODE_MEGAKERNEL, MODE_WAVEFRONT = range(3)
+RENDER_COUNTERS = 1
+
+
+class RtError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"rtgpu error {code}: {msg}")
+        self.code = code
+
+
+class RtPrim(C.Structure):
+    _fields_ = [("kind", C.c_uint32), ("mat", C.c_uint32), ("xform", C.c_uint32), ("flags", C.c_uint32),
+                ("object", C.c_uint32), ("aux0", C.c_uint32), ("aux1", C.c_uint32), ("reserved", C.c_uint32),
+                ("g", C.c_float * 12)]
+
+
+class RtXformOp(C.Structure):
+    _fields_ = [("kind", C.c_uint32), ("v", C.c_float * 3)]
+
+
+class RtXformChain(C.Structure):
+    _fields_ = [("first_op", C.c_uint32), ("n_ops", C.c_uint32)]
+
+
+class RtMaterial(C.Structure):
+    _fields_ = [("kind", C.c_uint32), ("tex0", C.c_uint32), ("tex1", C.c_uint32), ("reserved", C.c_uint32),
+                ("p", C.c_float * 4)]
+
+
+class RtTexture(C.Structure):
+    _fields_ = [("kind", C.c_uint32), ("a", C.c_uint32), ("b", C.c_uint32), ("reserved", C.c_uint32),
+                ("p", C.c_float * 4)]
+
+
+class RtPerlin(C.Structure):
+    _fields_ = [("rand_vec", (C.c_float * 4) * 256), ("perm_x", C.c_uint8 * 256), ("perm_y", C.c_uint8 * 256),
+                ("perm_z", C.c_uint8 * 256)]
+
+
+class RtImage(C.Structure):
+    _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("rgb8", C.POINTER(C.c_uint8))]
+
+
+class RtSky(C.Structure):
+    _fields_ = [("kind", C.c_uint32), ("image", C.c_uint32), ("color", C.c_float * 3)]
+
+
+class RtCamera(C.Structure):
+    _fields_ = [("origin", C.c_float * 3), ("horizontal", C.c_float * 3), ("vertical", C.c_float * 3),
+                ("lower_left_corner", C.c_float * 3), ("u", C.c_float * 3), ("v", C.c_float * 3),
+                ("lens_radius", C.c_float), ("time0", C.c_float), ("time1", C.c_float)]
+
+
+class RtFlatScene(C.Structure):
+    _fields_ = [("abi_version", C.c_uint32), ("n_prims", C.c_uint32), ("n_xform_ops", C.c_uint32),
+                ("n_xform_chains", C.c_uint32), ("n_materials", C.c_uint32), ("n_textures", C.c_uint32),
+                ("n_perlin", C.c_uint32), ("n_images", C.c_uint32),
+                ("prims", C.POINTER(RtPrim)), ("xform_ops", C.POINTER(RtXformOp)),
+                ("xform_chains", C.POINTER(RtXformChain)), ("materials", C.POINTER(RtMaterial)),
+                ("textures", C.POINTER(RtTexture)), ("perlin", C.POINTER(RtPerlin)), ("images", C.POINTER(RtImage)),
+                ("sky", RtSky), ("camera", RtCamera)]
+
+
+class RtBvhInfo(C.Structure):
+    _fields_ = [("n_nodes", C.c_uint32), ("n_world_prims", C.c_uint32), ("max_depth", C.c_uint32),
+                ("max_leaf_prims", C.c_uint32), ("sah_cost", C.c_float), ("node_bytes", C.c_uint32)]
+
+
+class RtHit(C.Structure):
+    _fields_ = [("prim", C.c_int32), ("t", C.c_float), ("p", C.c_float * 3), ("n", C.c_float * 3),
+                ("uv", C.c_float * 2), ("front_face", C.c_uint32)]
+
+
+HIT_DTYPE = np.dtype([("prim", "<i4"), ("t", "<f4"), ("p", "<f4", 3), ("n", "<f4", 3), ("uv", "<f4", 2),
+                      ("front_face", "<u4")])
+assert HIT_DTYPE.itemsize == C.sizeof(RtHit) == 44
+
+
+class RtRenderParams(C.Structure):
+    _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("spp_total", C.c_uint32),
+                ("sample_begin", C.c_uint32), ("sample_end", C.c_uint32), ("max_depth", C.c_uint32),
+                ("mode", C.c_uint32), ("flags", C.c_uint32), ("seed", C.c_uint64)]
+
+
+class RtStats(C.Structure):
+    _fields_ = [("paths", C.c_uint64), ("rays", C.c_uint64), ("node_visits", C.c_uint64), ("box_tests", C.c_uint64),
+                ("prim_tests", C.c_uint64), ("shade_calls", C.c_uint64), ("ms_kernel", C.c_double),
+                ("ms_total", C.c_double), ("launches", C.c_uint32), ("mode_used", C.c_uint32)]
+
+    def as_dict(self) -> dict:
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+# every symbol include/rtgpu.h declares
+EXPORTED_SYMBOLS = [
+    "rt_scene_create", "rt_scene_destroy", "rt_scene_bvh_info", "rt_closest_hit", "rt_closest_hit_device",
+    "rt_camera_get_rays", "rt_render_device", "rt_render", "rt_resolve_rgb8", "rt_measure_fp32_peak",
+    "rt_last_error", "rt_host_scene_build", "rt_host_scene_flat", "rt_host_scene_destroy",
+]
+
+_lib: Optional[C.CDLL] = None
+
+
+def load_library() -> C.CDLL:
+    """dlopen librtgpu.so (built in-tree by ray_tracing_in_one_weekend_b200.build). Fails loudly."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RtError(-2, f"{LIB_PATH} is missing — run `python -m ray_tracing_in_one_weekend_b200.build` "
+                          "(there is no CPU fallback)")
+    lib = C.CDLL(LIB_PATH)
+    vp, fp, u32, sz = C.c_void_p, C.POINTER(C.c_float), C.c_uint32, C.c_size_t
+    lib.rt_last_error.restype = C.c_char_p
+    lib.rt_scene_create.argtypes = [C.POINTER(RtFlatScene), C.c_int, C.POINTER(vp)]
+    lib.rt_scene_destroy.argtypes = [vp]
+    lib.rt_scene_destroy.restype = None
+    lib.rt_scene_bvh_info.argtypes = [vp, C.POINTER(RtBvhInfo)]
+    lib.rt_closest_hit.argtypes = [vp, vp, vp, vp, sz, C.c_float, C.c_float, vp]
+    lib.rt_closest_hit_device.argtypes = [vp, vp, vp, vp, sz, C.c_float, C.c_float, vp, vp]
+    lib.rt_camera_get_rays.argtypes = [C.POINTER(RtCamera), vp, sz, vp, vp]
+    lib.rt_render_device.argtypes = [vp, C.POINTER(RtRenderParams), vp, vp, C.POINTER(RtStats)]
+    lib.rt_render.argtypes = [vp, C.POINTER(RtRenderParams), vp, C.POINTER(RtStats)]
+    lib.rt_resolve_rgb8.argtypes = [vp, vp, u32, u32, vp]
+    lib.rt_measure_fp32_peak.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    lib.rt_host_scene_build.argtypes = [C.c_char_p, C.c_float, C.c_char_p, C.POINTER(vp)]
+    lib.rt_host_scene_flat.argtypes = [vp]
+    lib.rt_host_scene_flat.restype = C.POINTER(RtFlatScene)
+    lib.rt_host_scene_destroy.argtypes = [vp]
+    lib.rt_host_scene_destroy.restype = None
+    # test-only entry points (not part of rtgpu.h)
+    lib.rt_test_shade_cases.argtypes = [vp, vp, vp, vp, vp, u32, u32, vp]
+    lib.rt_test_texture_cases.argtypes = [vp, u32, vp, vp, u32, vp]
+    _lib = lib
+    return lib
+
+
+def _check(rc: int) -> None:
+    if rc != 0:
+        raise RtError(rc, load_library().rt_last_error().decode("utf-8", "replace"))
+
+
+def _ptr(a: Optional[np.ndarray]):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class HostScene:
+    """A scene built by the host API (csrc/scene_api.hpp) and flattened to an RtFlatScene.
+
+    `name` is one of the reference's scene functions (src/demo_scene.rs: test_sphere, sphere_scene,
+    simple_light_scene, cornell_box, final_scene) or a BASELINE.json config scene (textured,
+    cornell_box_solid, pbr_ibl, cover_defocus, cover_100k_motion, cover_4k_motion, furnace_<material>).
+    """
+
+    def __init__(self, name: str, aspect_ratio: float, asset_dir: str = ASSET_DIR):
+        self._lib = load_library()
+        h = C.c_void_p()
+        _check(self._lib.rt_host_scene_build(name.encode(), C.c_float(aspect_ratio), asset_dir.encode(), C.byref(h)))
+        self._h = h
+        self.name = name
+        self.aspect_ratio = aspect_ratio
+
+    @property
+    def flat(self) -> "C.POINTER(RtFlatScene)":
+        return self._lib.rt_host_scene_flat(self._h)
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self._lib.rt_host_scene_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def flat_to_numpy(flat_ptr) -> dict:
+    """Copy the POD arrays of an RtFlatScene into numpy structured arrays (for comparisons)."""
+    f = flat_ptr.contents
+
+    def arr(ptr, n, ctype):
+        if n == 0:
+            return np.zeros(0, dtype=np.uint8)
+        buf = C.string_at(ptr, n * C.sizeof(ctype))
+        return np.frombuffer(buf, dtype=np.uint8).copy()
+
+    out = {
+        "prims": arr(f.prims, f.n_prims, RtPrim), "xform_ops": arr(f.xform_ops, f.n_xform_ops, RtXformOp),
+        "xform_chains": arr(f.xform_chains, f.n_xform_chains, RtXformChain),
+        "materials": arr(f.materials, f.n_materials, RtMaterial), "textures": arr(f.textures, f.n_textures, RtTexture),
+        "perlin": arr(f.perlin, f.n_perlin, RtPerlin),
+        "sky": np.frombuffer(bytes(f.sky), dtype=np.uint8).copy(),
+        "camera": np.frombuffer(bytes(f.camera), dtype=np.uint8).copy(),
+    }
+    imgs = []
+    for i in range(f.n_images):
+        im = f.images[i]
+        imgs.append(np.frombuffer(C.string_at(im.rgb8, im.width * im.height * 3), dtype=np.uint8)
+                    .reshape(im.height, im.width, 3).copy())
+    out["images"] = imgs
+    return out
+
+
+def camera_get_rays(cam: RtCamera, uv: np.ndarray):
+    """Host-side Camera::get_ray (camera.rs:40-46) for an (n,2) float32 array of (u,v)."""
+    lib = load_library()
+    uv = np.ascontiguousarray(uv, dtype=np.float32)
+    n = uv.shape[0]
+    o = np.empty((n, 3), np.float32)
+    d = np.empty((n, 3), np.float32)
+    _check(lib.rt_camera_get_rays(C.byref(cam), _ptr(uv), n, _ptr(o), _ptr(d)))
+    return o, d
+
+
+def pixel_center_uv(width: int, height: int) -> np.ndarray:
+    """u=(i+0.5)/nx, v=(j+0.5)/ny for every pixel, j=0 bottom, row-major (j*width+i), float32 math."""
+    i = (np.arange(width, dtype=np.float32) + np.float32(0.5)) / np.float32(width)
+    j = (np.arange(height, dtype=np.float32) + np.float32(0.5)) / np.float32(height)
+    uv = np.empty((height, width, 2), np.float32)
+    uv[..., 0] = i[None, :]
+    uv[..., 1] = j[:, None]
+    return uv.reshape(-1, 2)
+
+
+class Scene:
+    """Device scene handle (rt_scene_create). Requires a CUDA device."""
+
+    def __init__(self, flat_ptr, device: int = 0):
+        self._lib = load_library()
+        h = C.c_void_p()
+        _check(self._lib.rt_scene_create(flat_ptr, device, C.byref(h)))
+        self._h = h
+        self.device = device
+        self.camera = RtCamera.from_buffer_copy(bytes(flat_ptr.contents.camera))
+
+    @classmethod
+    def from_name(cls, name: str, aspect_ratio: float, device: int = 0) -> "Scene":
+        hs = HostScene(name, aspect_ratio)
+        try:
+            return cls(hs.flat, device)
+        finally:
+            hs.close()
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self._lib.rt_scene_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def bvh_info(self) -> RtBvhInfo:
+        info = RtBvhInfo()
+        _check(self._lib.rt_scene_bvh_info(self._h, C.byref(info)))
+        return info
+
+    def closest_hit(self, o: np.ndarray, d: np.ndarray, t_min: float = 1e-3, t_max: float = 3.4028234663852886e38,
+                    times: Optional[np.ndarray] = None) -> np.ndarray:
+        """world.hit over a batch of rays in HOST memory (main.rs:44). Returns a HIT_DTYPE array."""
+        o = np.ascontiguousarray(o, dtype=np.float32)
+        d = np.ascontiguousarray(d, dtype=np.float32)
+        n = o.shape[0]
+        if times is not None:
+            times = np.ascontiguousarray(times, dtype=np.float32)
+        out = np.zeros(n, dtype=HIT_DTYPE)
+        _check(self._lib.rt_closest_hit(self._h, _ptr(o), _ptr(d), _ptr(times), n, C.c_float(t_min), C.c_float(t_max),
+                                        _ptr(out)))
+        return out
+
+    def make_params(self, width: int, height: int, spp: int, *, sample_begin: int = 0,
+                    sample_end: Optional[int] = None, spp_total: Optional[int] = None, max_depth: int = 50,
+                    seed: int = 95, mode: int = MODE_AUTO, flags: int = 0) -> RtRenderParams:
+        se = spp if sample_end is None else sample_end
+        return RtRenderParams(width, height, spp if spp_total is None else spp_total, sample_begin, se, max_depth,
+                              mode, flags, seed)
+
+    def render(self, width: int, height: int, spp: int, **kw):
+        """Host-buffer render: returns (linear mean image (H,W,3) float32 with row 0 = bottom, RtStats)."""
+        p = self.make_params(width, height, spp, **kw)
+        out = np.empty((height, width, 3), np.float32)
+        st = RtStats()
+        _check(self._lib.rt_render(self._h, C.byref(p), _ptr(out), C.byref(st)))
+        return out, st
+
+    def render_device(self, params: RtRenderParams, accum_ptr: int, stream_ptr: int = 0, want_stats: bool = True):
+        """Adds radiance sums of the sample range to a DEVICE buffer (e.g. a torch tensor's data_ptr())."""
+        st = RtStats() if want_stats else None
+        _check(self._lib.rt_render_device(self._h, C.byref(params), C.c_void_p(accum_ptr),
+                                          C.c_void_p(stream_ptr) if stream_ptr else None,
+                                          C.byref(st) if st is not None else None))
+        return st
+
+    def resolve_rgb8(self, mean: np.ndarray) -> np.ndarray:
+        """powf(0.5), *255.99 as u8, vertical flip (main.rs:98-105,127). Returns (H,W,3) uint8, row 0 = top."""
+        mean = np.ascontiguousarray(mean, dtype=np.float32)
+        h, w = mean.shape[:2]
+        out = np.empty((h, w, 3), np.uint8)
+        _check(self._lib.rt_resolve_rgb8(self._h, _ptr(mean), w, h, _ptr(out)))
+        return out
+
+
+def measure_fp32_peak(device: int = 0):
+    lib = load_library()
+    a, b = C.c_double(), C.c_double()
+    _check(lib.rt_measure_fp32_peak(device, C.byref(a), C.byref(b)))
+    return a.value, b.value

@@ -1,0 +1,74 @@
+"""Build recipe for librtgpu.so (in-tree, sm_100a only).
+
+    python -m ray_tracing_in_one_weekend_b200.build        # or build_all() from __graft_entry__.build()
+
+Host translation units are compiled with -ffp-contract=off and the CUDA unit with -fmad=false so
+that every float operation is rounded individually, in the reference's operation order (see
+csrc/rt_device.cuh "NUMERICS CONTRACT").  nvcc cross-compiles without a GPU.
+"""
+from __future__ import annotations
+
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+LIB = os.path.join(HERE, "librtgpu.so")
+
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+CXX = os.environ.get("CXX", "g++")
+
+HOST_SRCS = ["scene_api.cpp", "demo_scene.cpp", "bvh_build.cpp"]
+CUDA_SRCS = ["rtgpu.cu"]
+HEADERS = ["scene_api.hpp", "bvh_build.hpp", "device_types.h", "rt_device.cuh", "kernels.cuh",
+           os.path.join("..", "..", "include", "rtgpu.h")]
+
+HOST_FLAGS = ["-std=c++17", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-Wall"]
+NVCC_FLAGS = [
+    "-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
+    "-fmad=false", "-prec-div=true", "-prec-sqrt=true", "-ftz=false",
+    "-Xcompiler", "-fPIC,-ffp-contract=off,-fno-fast-math", "-Xptxas", "-v",
+]
+
+
+def _stale(target: str, deps: list[str]) -> bool:
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+
+
+def _run(cmd: list[str]) -> str:
+    r = subprocess.run(cmd, cwd=CSRC, capture_output=True, text=True)
+    if r.returncode != 0:
+        sys.stderr.write(r.stdout + r.stderr)
+        raise RuntimeError("build failed: " + " ".join(cmd))
+    return r.stdout + r.stderr
+
+
+def build_all(force: bool = False, verbose: bool = False) -> str:
+    hdrs = [os.path.join(CSRC, h) for h in HEADERS]
+    objs = []
+    log = []
+    for src in HOST_SRCS:
+        obj = os.path.join(CSRC, src.replace(".cpp", ".o"))
+        if force or _stale(obj, [os.path.join(CSRC, src)] + hdrs):
+            log.append(_run([CXX] + HOST_FLAGS + ["-c", src, "-o", obj]))
+        objs.append(obj)
+    for src in CUDA_SRCS:
+        obj = os.path.join(CSRC, src.replace(".cu", ".o"))
+        if force or _stale(obj, [os.path.join(CSRC, src)] + hdrs):
+            log.append(_run([NVCC] + NVCC_FLAGS + ["-c", src, "-o", obj]))
+        objs.append(obj)
+    if force or _stale(LIB, objs):
+        log.append(_run([NVCC, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"]))
+    out = "".join(log)
+    if verbose and out:
+        print(out)
+    return LIB
+
+
+if __name__ == "__main__":
+    build_all(force="--force" in sys.argv, verbose=True)
+    print(LIB)

@@ -1,0 +1,621 @@
+// librtgpu.so — C ABI entry points (include/rtgpu.h): scene upload, batch closest hit, render,
+// resolve, FP32 peak probe.  There is no CPU fallback: without a usable CUDA device every compute
+// entry point fails with RT_ERR_CUDA.
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "bvh_build.hpp"
+#include "kernels.cuh"
+#include "scene_api.hpp"
+
+using namespace rtb;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) {
+    g_err = msg;
+    return code;
+}
+#define CU_TRY(expr)                                                                                        \
+    do {                                                                                                    \
+        cudaError_t e__ = (expr);                                                                           \
+        if (e__ != cudaSuccess)                                                                             \
+            return fail(RT_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e__));                 \
+    } while (0)
+
+struct RtScene {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    DeviceScene ds{};
+    std::vector<void*> allocs;
+    std::vector<cudaArray_t> arrays;
+    std::vector<cudaTextureObject_t> texobjs;
+    RtBvhInfo bvh{};
+    RtCamera camera{};
+    // render scratch
+    unsigned int* work_counter = nullptr;
+    unsigned long long* stats = nullptr;
+    float* accum = nullptr;
+    size_t accum_floats = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    int mega_blocks_per_sm = 0, mega_blocks_per_sm_cnt = 0, sm_count = 0;
+
+    ~RtScene() {
+        cudaSetDevice(device);
+        for (auto t : texobjs) cudaDestroyTextureObject(t);
+        for (auto a : arrays) cudaFreeArray(a);
+        for (auto p : allocs) cudaFree(p);
+        if (accum) cudaFree(accum);
+        if (ev0) cudaEventDestroy(ev0);
+        if (ev1) cudaEventDestroy(ev1);
+        if (stream) cudaStreamDestroy(stream);
+    }
+};
+
+namespace {
+
+template <class T>
+cudaError_t upload(RtScene* s, const T* host, size_t n, const T** dev) {
+    *dev = nullptr;
+    void* p = nullptr;
+    size_t bytes = std::max<size_t>(n, 1) * sizeof(T);
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) return e;
+    s->allocs.push_back(p);
+    if (n) {
+        e = cudaMemcpy(p, host, n * sizeof(T), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) return e;
+    }
+    *dev = reinterpret_cast<const T*>(p);
+    return cudaSuccess;
+}
+
+std::string validate(const RtFlatScene* d) {
+    if (!d) return "desc is NULL";
+    if (d->abi_version != RT_ABI_VERSION) return "abi_version mismatch";
+    if (d->n_prims == 0 || !d->prims) return "scene has no primitives";
+    if (d->n_xform_chains == 0 || !d->xform_chains || d->xform_chains[0].n_ops != 0) return "xform chain 0 must be the identity";
+    if (d->n_prims > LEAF_FIRST_MASK) return "too many primitives";
+    if (d->n_xform_chains > 0xffffu) return "too many transform chains (max 65535)";
+    for (uint32_t i = 0; i < d->n_xform_chains; i++) {
+        const RtXformChain& c = d->xform_chains[i];
+        if (c.n_ops > (uint32_t)MAX_CHAIN) return "transform chain deeper than 4";
+        if ((uint64_t)c.first_op + c.n_ops > d->n_xform_ops) return "transform chain out of range";
+    }
+    for (uint32_t i = 0; i < d->n_xform_ops; i++)
+        if (d->xform_ops[i].kind > RT_XF_ROTATE_Y) return "bad transform op kind";
+    for (uint32_t i = 0; i < d->n_textures; i++) {
+        const RtTexture& t = d->textures[i];
+        if (t.kind > RT_TEX_IMAGE) return "bad texture kind";
+        if (t.kind == RT_TEX_CHECKER && (t.a >= d->n_textures || t.b >= d->n_textures)) return "checker child out of range";
+        if (t.kind == RT_TEX_PERLIN && t.a >= d->n_perlin) return "perlin table out of range";
+        if (t.kind == RT_TEX_IMAGE && t.a >= d->n_images) return "image out of range";
+    }
+    for (uint32_t i = 0; i < d->n_images; i++)
+        if (!d->images[i].rgb8 || d->images[i].width == 0 || d->images[i].height == 0) return "empty image";
+    for (uint32_t i = 0; i < d->n_materials; i++) {
+        const RtMaterial& m = d->materials[i];
+        if (m.kind > RT_MAT_DISNEY_CLEARCOAT) return "bad material kind";
+        bool t0 = !(m.kind == RT_MAT_METAL || m.kind == RT_MAT_DIELECTRIC || m.kind == RT_MAT_DISNEY_CLEARCOAT);
+        if (t0 && m.tex0 >= d->n_textures) return "material texture out of range";
+        if (m.kind == RT_MAT_ROUGH_PLASTIC && m.tex1 >= d->n_textures) return "material texture out of range";
+    }
+    for (uint32_t i = 0; i < d->n_prims; i++) {
+        const RtPrim& p = d->prims[i];
+        if (p.kind > RT_PRIM_MEDIUM) return "bad primitive kind";
+        if (p.mat >= d->n_materials) return "primitive material out of range";
+        if (p.xform >= d->n_xform_chains) return "primitive transform out of range";
+        if (p.kind == RT_PRIM_MEDIUM) {
+            if (p.xform != 0 || (p.flags & RT_PRIM_FLAG_BOUNDARY_ONLY)) return "medium under a transform / as a boundary is unsupported";
+            if (p.aux1 == 0 || (uint64_t)p.aux0 + p.aux1 > d->n_prims) return "medium boundary out of range";
+            for (uint32_t k = 0; k < p.aux1; k++) {
+                const RtPrim& b = d->prims[p.aux0 + k];
+                if (!(b.flags & RT_PRIM_FLAG_BOUNDARY_ONLY) || b.kind == RT_PRIM_MEDIUM) return "medium boundary must be boundary-only geometry";
+            }
+            if (d->materials[p.mat].kind != RT_MAT_ISOTROPIC) return "medium material must be Isotropic";
+        }
+    }
+    if (d->sky.kind > RT_SKY_CONSTANT) return "bad sky kind";
+    if (d->sky.kind == RT_SKY_ENVMAP && d->sky.image >= d->n_images) return "sky image out of range";
+    return "";
+}
+
+// does texture i (transitively) read uv?
+bool tex_needs_uv(const RtFlatScene* d, uint32_t i, int depth = 0) {
+    const RtTexture& t = d->textures[i];
+    if (t.kind == RT_TEX_IMAGE) return true;
+    if (t.kind == RT_TEX_CHECKER && depth < 8) return tex_needs_uv(d, t.a, depth + 1) || tex_needs_uv(d, t.b, depth + 1);
+    return false;
+}
+
+DevPrim make_dev_prim(const RtFlatScene* d, uint32_t flat, std::vector<DevMotion>& motion, const std::vector<uint32_t>& flat_to_dev) {
+    const RtPrim& p = d->prims[flat];
+    DevPrim q{};
+    q.mat = p.mat;
+    q.kfx = (p.kind & 0xffu) | ((p.flags & 0xffu) << 8) | (p.xform << 16);
+    q.flat = flat;
+    auto bits = [](uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; };
+    auto ubits = [](float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; };
+    switch (p.kind) {
+        case RT_PRIM_SPHERE:
+            q.g0 = p.g[0]; q.g1 = p.g[1]; q.g2 = p.g[2]; q.g3 = p.g[3];
+            break;
+        case RT_PRIM_MOVING_SPHERE: {
+            q.g0 = p.g[0]; q.g1 = p.g[1]; q.g2 = p.g[2]; q.g3 = p.g[3];
+            DevMotion m{};
+            m.dcx = p.g[4] - p.g[0]; m.dcy = p.g[5] - p.g[1]; m.dcz = p.g[6] - p.g[2];
+            m.time0 = p.g[7];
+            m.dt = p.g[8] - p.g[7];
+            q.x = (uint32_t)motion.size();
+            motion.push_back(m);
+            break;
+        }
+        case RT_PRIM_XYRECT:  // plane z; a = x, b = y
+            q.g0 = p.g[2]; q.g1 = p.g[0]; q.g2 = p.g[3]; q.g3 = p.g[1]; q.x = ubits(p.g[4]);
+            break;
+        case RT_PRIM_XZRECT:  // plane y; a = x, b = z
+            q.g0 = p.g[1]; q.g1 = p.g[0]; q.g2 = p.g[3]; q.g3 = p.g[2]; q.x = ubits(p.g[5]);
+            break;
+        case RT_PRIM_YZRECT:  // plane x; a = y, b = z
+            q.g0 = p.g[0]; q.g1 = p.g[1]; q.g2 = p.g[4]; q.g3 = p.g[2]; q.x = ubits(p.g[5]);
+            break;
+        case RT_PRIM_MEDIUM:
+            q.g0 = p.g[0];
+            q.g1 = bits(flat_to_dev[p.aux0]);
+            q.g2 = bits(p.aux1);
+            break;
+    }
+    return q;
+}
+
+int env_int(const char* name, int dflt) {
+    const char* v = std::getenv(name);
+    return v ? std::atoi(v) : dflt;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* rt_last_error(void) { return g_err.c_str(); }
+
+int rt_scene_create(const RtFlatScene* desc, int device, RtScene** out) {
+    if (!out) return fail(RT_ERR_ARG, "out is NULL");
+    *out = nullptr;
+    std::string why = validate(desc);
+    if (!why.empty()) return fail(RT_ERR_ARG, why);
+    int n_dev = 0;
+    CU_TRY(cudaGetDeviceCount(&n_dev));
+    if (device < 0 || device >= n_dev) return fail(RT_ERR_CUDA, "no such CUDA device");
+    CU_TRY(cudaSetDevice(device));
+
+    BvhBuildResult bvh;
+    try {
+        build_bvh4(*desc, (uint32_t)env_int("RT_LEAF_MAX", 4), bvh);
+    } catch (const std::exception& e) {
+        return fail(RT_ERR_ARG, e.what());
+    }
+
+    std::unique_ptr<RtScene> s(new RtScene());
+    s->device = device;
+    CU_TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    CU_TRY(cudaEventCreate(&s->ev0));
+    CU_TRY(cudaEventCreate(&s->ev1));
+    cudaDeviceProp prop;
+    CU_TRY(cudaGetDeviceProperties(&prop, device));
+    s->sm_count = prop.multiProcessorCount;
+
+    // device primitive array: world primitives in BVH leaf order, then boundary-only primitives in flat order
+    std::vector<uint32_t> order = bvh.leaf_order;
+    for (uint32_t i = 0; i < desc->n_prims; i++)
+        if (desc->prims[i].flags & RT_PRIM_FLAG_BOUNDARY_ONLY) order.push_back(i);
+    std::vector<uint32_t> flat_to_dev(desc->n_prims, 0xffffffffu);
+    for (uint32_t k = 0; k < order.size(); k++) flat_to_dev[order[k]] = k;
+    std::vector<DevMotion> motion;
+    std::vector<DevPrim> prims(order.size());
+    bool has_media = false;
+    for (uint32_t k = 0; k < order.size(); k++) {
+        prims[k] = make_dev_prim(desc, order[k], motion, flat_to_dev);
+        has_media |= desc->prims[order[k]].kind == RT_PRIM_MEDIUM;
+    }
+    // boundary ranges must stay contiguous on the device
+    for (uint32_t i = 0; i < desc->n_prims; i++)
+        if (desc->prims[i].kind == RT_PRIM_MEDIUM)
+            for (uint32_t k = 1; k < desc->prims[i].aux1; k++)
+                if (flat_to_dev[desc->prims[i].aux0 + k] != flat_to_dev[desc->prims[i].aux0] + k)
+                    return fail(RT_ERR_ARG, "medium boundary primitives are not contiguous");
+
+    std::vector<DevXformOp> ops(desc->n_xform_ops);
+    for (uint32_t i = 0; i < desc->n_xform_ops; i++)
+        ops[i] = DevXformOp{desc->xform_ops[i].kind, desc->xform_ops[i].v[0], desc->xform_ops[i].v[1], desc->xform_ops[i].v[2]};
+    std::vector<DevXformChain> chains(desc->n_xform_chains);
+    for (uint32_t i = 0; i < desc->n_xform_chains; i++) chains[i] = DevXformChain{desc->xform_chains[i].first_op, desc->xform_chains[i].n_ops};
+    std::vector<DevMaterial> mats(desc->n_materials);
+    for (uint32_t i = 0; i < desc->n_materials; i++) {
+        const RtMaterial& m = desc->materials[i];
+        bool t0 = !(m.kind == RT_MAT_METAL || m.kind == RT_MAT_DIELECTRIC || m.kind == RT_MAT_DISNEY_CLEARCOAT);
+        uint32_t flags = 0;
+        if (t0 && tex_needs_uv(desc, m.tex0)) flags |= 1u;
+        if (m.kind == RT_MAT_ROUGH_PLASTIC && tex_needs_uv(desc, m.tex1)) flags |= 1u;
+        mats[i] = DevMaterial{m.kind, m.tex0, m.tex1, flags, m.p[0], m.p[1], m.p[2], m.p[3]};
+    }
+    std::vector<DevTexture> texs(desc->n_textures);
+    for (uint32_t i = 0; i < desc->n_textures; i++) {
+        const RtTexture& t = desc->textures[i];
+        texs[i] = DevTexture{t.kind, t.a, t.b, 0, t.p[0], t.p[1], t.p[2], t.p[3]};
+    }
+    CU_TRY(upload(s.get(), bvh.nodes.data(), bvh.nodes.size(), &s->ds.nodes));
+    CU_TRY(upload(s.get(), prims.data(), prims.size(), &s->ds.prims));
+    CU_TRY(upload(s.get(), motion.data(), motion.size(), &s->ds.motion));
+    CU_TRY(upload(s.get(), ops.data(), ops.size(), &s->ds.ops));
+    CU_TRY(upload(s.get(), chains.data(), chains.size(), &s->ds.chains));
+    CU_TRY(upload(s.get(), mats.data(), mats.size(), &s->ds.mats));
+    CU_TRY(upload(s.get(), texs.data(), texs.size(), &s->ds.texs));
+
+    // Perlin tables: gradients behind a texture object (texel fetch), permutations as bytes
+    {
+        std::vector<float4> grad(std::max<size_t>(1, (size_t)desc->n_perlin * 256));
+        std::vector<uint8_t> perm(std::max<size_t>(1, (size_t)desc->n_perlin * 768));
+        for (uint32_t t = 0; t < desc->n_perlin; t++) {
+            const RtPerlin& p = desc->perlin[t];
+            for (int k = 0; k < 256; k++) {
+                grad[t * 256 + k] = make_float4(p.rand_vec[k][0], p.rand_vec[k][1], p.rand_vec[k][2], 0.0f);
+                perm[t * 768 + k] = p.perm_x[k];
+                perm[t * 768 + 256 + k] = p.perm_y[k];
+                perm[t * 768 + 512 + k] = p.perm_z[k];
+            }
+        }
+        const float4* dgrad = nullptr;
+        CU_TRY(upload(s.get(), grad.data(), grad.size(), &dgrad));
+        CU_TRY(upload(s.get(), perm.data(), perm.size(), &s->ds.perlin_perm));
+        cudaResourceDesc rd{};
+        rd.resType = cudaResourceTypeLinear;
+        rd.res.linear.devPtr = const_cast<float4*>(dgrad);
+        rd.res.linear.desc = cudaCreateChannelDesc<float4>();
+        rd.res.linear.sizeInBytes = grad.size() * sizeof(float4);
+        cudaTextureDesc td{};
+        td.readMode = cudaReadModeElementType;
+        cudaTextureObject_t to = 0;
+        CU_TRY(cudaCreateTextureObject(&to, &rd, &td, nullptr));
+        s->texobjs.push_back(to);
+        s->ds.perlin_grad = to;
+    }
+    // images: uchar4 CUDA arrays behind point-sampled, clamped, unnormalised texture objects
+    {
+        std::vector<DevImage> imgs(desc->n_images);
+        for (uint32_t i = 0; i < desc->n_images; i++) {
+            const RtImage& im = desc->images[i];
+            std::vector<uchar4> rgba((size_t)im.width * im.height);
+            for (size_t k = 0; k < rgba.size(); k++) rgba[k] = make_uchar4(im.rgb8[3 * k], im.rgb8[3 * k + 1], im.rgb8[3 * k + 2], 255);
+            cudaChannelFormatDesc cd = cudaCreateChannelDesc<uchar4>();
+            cudaArray_t arr = nullptr;
+            CU_TRY(cudaMallocArray(&arr, &cd, im.width, im.height));
+            s->arrays.push_back(arr);
+            CU_TRY(cudaMemcpy2DToArray(arr, 0, 0, rgba.data(), (size_t)im.width * 4, (size_t)im.width * 4, im.height, cudaMemcpyHostToDevice));
+            cudaResourceDesc rd{};
+            rd.resType = cudaResourceTypeArray;
+            rd.res.array.array = arr;
+            cudaTextureDesc td{};
+            td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;
+            td.filterMode = cudaFilterModePoint;
+            td.readMode = cudaReadModeElementType;
+            td.normalizedCoords = 0;
+            cudaTextureObject_t to = 0;
+            CU_TRY(cudaCreateTextureObject(&to, &rd, &td, nullptr));
+            s->texobjs.push_back(to);
+            imgs[i] = DevImage{to, im.width, im.height};
+        }
+        CU_TRY(upload(s.get(), imgs.data(), imgs.size(), &s->ds.images));
+    }
+    s->ds.sky = DevSky{desc->sky.kind, desc->sky.image, desc->sky.color[0], desc->sky.color[1], desc->sky.color[2]};
+    const RtCamera& c = desc->camera;
+    auto v3 = [](const float* p) { return V3f{p[0], p[1], p[2]}; };
+    s->ds.cam = DevCamera{v3(c.origin), v3(c.horizontal), v3(c.vertical), v3(c.lower_left_corner), v3(c.u), v3(c.v), c.lens_radius, c.time0, c.time1};
+    s->ds.n_world_prims = bvh.n_world_prims;
+    s->ds.n_prims = (uint32_t)prims.size();
+    s->ds.has_media = has_media ? 1u : 0u;
+    s->camera = c;
+    s->bvh = RtBvhInfo{(uint32_t)bvh.nodes.size(), bvh.n_world_prims, bvh.max_depth, bvh.max_leaf_prims, bvh.sah_cost, (uint32_t)sizeof(BvhNode4)};
+    if (bvh.max_depth * 3u + 4u > (uint32_t)STACK_SIZE) return fail(RT_ERR_UNSUPPORTED, "BVH too deep for the traversal stack");
+
+    void* p = nullptr;
+    CU_TRY(cudaMalloc(&p, sizeof(unsigned int)));
+    s->allocs.push_back(p);
+    s->work_counter = (unsigned int*)p;
+    CU_TRY(cudaMalloc(&p, 8 * sizeof(unsigned long long)));
+    s->allocs.push_back(p);
+    s->stats = (unsigned long long*)p;
+    // the traversal stack lives in local memory: make sure L1 is preferred over shared memory
+    CU_TRY(cudaFuncSetAttribute(k_render_mega<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 0));
+    CU_TRY(cudaFuncSetAttribute(k_render_mega<true>, cudaFuncAttributePreferredSharedMemoryCarveout, 0));
+    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->mega_blocks_per_sm, k_render_mega<false>, MEGA_THREADS, 0));
+    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->mega_blocks_per_sm_cnt, k_render_mega<true>, MEGA_THREADS, 0));
+    if (s->mega_blocks_per_sm < 1 || s->mega_blocks_per_sm_cnt < 1) return fail(RT_ERR_CUDA, "render kernel does not fit on an SM");
+    CU_TRY(cudaDeviceSynchronize());
+    *out = s.release();
+    return RT_OK;
+}
+
+void rt_scene_destroy(RtScene* scene) { delete scene; }
+
+int rt_scene_bvh_info(const RtScene* scene, RtBvhInfo* out) {
+    if (!scene || !out) return fail(RT_ERR_ARG, "NULL argument");
+    *out = scene->bvh;
+    return RT_OK;
+}
+
+int rt_closest_hit_device(RtScene* s, const float* o, const float* d, const float* times, size_t n, float t_min, float t_max,
+                          RtHit* out, void* cuda_stream) {
+    if (!s || !o || !d || !out) return fail(RT_ERR_ARG, "NULL argument");
+    if (n == 0) return RT_OK;
+    CU_TRY(cudaSetDevice(s->device));
+    cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : s->stream;
+    unsigned blocks = (unsigned)((n + 127) / 128);
+    k_closest_hit_batch<<<blocks, 128, 0, st>>>(s->ds, o, d, times, n, t_min, t_max, out);
+    CU_TRY(cudaGetLastError());
+    return RT_OK;
+}
+
+int rt_closest_hit(RtScene* s, const float* o, const float* d, const float* times, size_t n, float t_min, float t_max, RtHit* out) {
+    if (!s || !o || !d || !out) return fail(RT_ERR_ARG, "NULL argument");
+    if (n == 0) return RT_OK;
+    CU_TRY(cudaSetDevice(s->device));
+    float *d_o = nullptr, *d_d = nullptr, *d_t = nullptr;
+    RtHit* d_out = nullptr;
+    auto cleanup = [&]() {
+        cudaFree(d_o); cudaFree(d_d); cudaFree(d_t); cudaFree(d_out);
+    };
+    cudaError_t e;
+    if ((e = cudaMalloc(&d_o, n * 12)) != cudaSuccess || (e = cudaMalloc(&d_d, n * 12)) != cudaSuccess ||
+        (e = cudaMalloc(&d_out, n * sizeof(RtHit))) != cudaSuccess || (times && (e = cudaMalloc(&d_t, n * 4)) != cudaSuccess)) {
+        cleanup();
+        return fail(RT_ERR_CUDA, std::string("cudaMalloc: ") + cudaGetErrorString(e));
+    }
+    cudaMemcpyAsync(d_o, o, n * 12, cudaMemcpyHostToDevice, s->stream);
+    cudaMemcpyAsync(d_d, d, n * 12, cudaMemcpyHostToDevice, s->stream);
+    if (times) cudaMemcpyAsync(d_t, times, n * 4, cudaMemcpyHostToDevice, s->stream);
+    int rc = rt_closest_hit_device(s, d_o, d_d, d_t, n, t_min, t_max, d_out, s->stream);
+    if (rc == RT_OK) {
+        cudaMemcpyAsync(out, d_out, n * sizeof(RtHit), cudaMemcpyDeviceToHost, s->stream);
+        e = cudaStreamSynchronize(s->stream);
+        if (e != cudaSuccess) rc = fail(RT_ERR_CUDA, std::string("closest hit: ") + cudaGetErrorString(e));
+    }
+    cleanup();
+    return rc;
+}
+
+int rt_camera_get_rays(const RtCamera* cam, const float* uv, size_t n, float* o_xyz, float* d_xyz) {
+    if (!cam || !uv || !o_xyz || !d_xyz) return fail(RT_ERR_ARG, "NULL argument");
+    // Camera::get_ray (camera.rs:40-46) on the host, glam operation order (scene_api.hpp V3)
+    V3 origin(cam->origin[0], cam->origin[1], cam->origin[2]);
+    V3 h(cam->horizontal[0], cam->horizontal[1], cam->horizontal[2]);
+    V3 v(cam->vertical[0], cam->vertical[1], cam->vertical[2]);
+    V3 llc(cam->lower_left_corner[0], cam->lower_left_corner[1], cam->lower_left_corner[2]);
+    for (size_t i = 0; i < n; i++) {
+        V3 dir = normalize(llc + uv[2 * i] * h + uv[2 * i + 1] * v - origin);
+        o_xyz[3 * i] = origin.x; o_xyz[3 * i + 1] = origin.y; o_xyz[3 * i + 2] = origin.z;
+        d_xyz[3 * i] = dir.x; d_xyz[3 * i + 1] = dir.y; d_xyz[3 * i + 2] = dir.z;
+    }
+    return RT_OK;
+}
+
+int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* cuda_stream, RtStats* stats) {
+    if (!s || !rp || !accum) return fail(RT_ERR_ARG, "NULL argument");
+    if (rp->width == 0 || rp->height == 0 || rp->sample_end < rp->sample_begin) return fail(RT_ERR_ARG, "bad render params");
+    if (rp->mode == RT_MODE_WAVEFRONT) return fail(RT_ERR_UNSUPPORTED, "wavefront mode not built yet");
+    auto wall0 = std::chrono::steady_clock::now();
+    CU_TRY(cudaSetDevice(s->device));
+    cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : s->stream;
+    const bool count = (rp->flags & RT_RENDER_COUNTERS) != 0;
+    const uint32_t n_samples = rp->sample_end - rp->sample_begin;
+    RenderArgs a{};
+    a.width = rp->width;
+    a.height = rp->height;
+    a.s_begin = rp->sample_begin;
+    a.s_end = rp->sample_end;
+    a.max_depth = rp->max_depth;
+    a.tiles_x = (rp->width + 7) / 8;
+    a.n_tiles = a.tiles_x * ((rp->height + 3) / 4);
+    a.seed = rp->seed;
+    a.accum = accum;
+    a.work_counter = s->work_counter;
+    a.stats = s->stats;
+    const int bps = count ? s->mega_blocks_per_sm_cnt : s->mega_blocks_per_sm;
+    const uint32_t grid = (uint32_t)(s->sm_count * bps);
+    const uint32_t resident_warps = grid * (MEGA_THREADS / 32);
+    // split the sample range into chunks so that there are >= ~24 work units per resident warp
+    // (bounds the tail), but never chunks shorter than 8 samples
+    uint32_t want_units = resident_warps * (uint32_t)env_int("RT_UNITS_PER_WARP", 24);
+    uint32_t n_chunks = (want_units + a.n_tiles - 1) / a.n_tiles;
+    n_chunks = std::max(1u, std::min(n_chunks, std::max(1u, n_samples / 8u)));
+    a.chunk_spp = (n_samples + n_chunks - 1) / n_chunks;
+    if (a.chunk_spp == 0) a.chunk_spp = 1;
+    a.n_chunks = n_samples ? (n_samples + a.chunk_spp - 1) / a.chunk_spp : 0;
+    uint32_t launches = 0;
+    if (n_samples) {
+        CU_TRY(cudaMemsetAsync(s->work_counter, 0, sizeof(unsigned int), st));
+        CU_TRY(cudaMemsetAsync(s->stats, 0, 8 * sizeof(unsigned long long), st));
+        if (stats) CU_TRY(cudaEventRecord(s->ev0, st));
+        if (count)
+            k_render_mega<true><<<grid, MEGA_THREADS, 0, st>>>(s->ds, a);
+        else
+            k_render_mega<false><<<grid, MEGA_THREADS, 0, st>>>(s->ds, a);
+        CU_TRY(cudaGetLastError());
+        launches = 1;
+        if (stats) CU_TRY(cudaEventRecord(s->ev1, st));
+    }
+    if (stats) {
+        std::memset(stats, 0, sizeof(*stats));
+        unsigned long long h[8] = {0};
+        if (n_samples) {
+            CU_TRY(cudaMemcpyAsync(h, s->stats, sizeof(h), cudaMemcpyDeviceToHost, st));
+            CU_TRY(cudaStreamSynchronize(st));
+            float ms = 0.0f;
+            CU_TRY(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+            stats->ms_kernel = ms;
+        }
+        stats->paths = (uint64_t)rp->width * rp->height * n_samples;
+        stats->rays = h[0];
+        stats->shade_calls = h[1];
+        stats->node_visits = h[2];
+        stats->box_tests = h[3];
+        stats->prim_tests = h[4];
+        stats->launches = launches;
+        stats->mode_used = RT_MODE_MEGAKERNEL;
+        stats->ms_total = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count();
+    }
+    return RT_OK;
+}
+
+int rt_render(RtScene* s, const RtRenderParams* rp, float* out_rgb_mean, RtStats* stats) {
+    if (!s || !rp || !out_rgb_mean) return fail(RT_ERR_ARG, "NULL argument");
+    auto wall0 = std::chrono::steady_clock::now();
+    CU_TRY(cudaSetDevice(s->device));
+    size_t nf = (size_t)rp->width * rp->height * 3;
+    if (nf == 0) return fail(RT_ERR_ARG, "empty image");
+    if (s->accum_floats < nf) {
+        if (s->accum) cudaFree(s->accum);
+        s->accum = nullptr;
+        s->accum_floats = 0;
+        CU_TRY(cudaMalloc(&s->accum, nf * sizeof(float)));
+        s->accum_floats = nf;
+    }
+    CU_TRY(cudaMemsetAsync(s->accum, 0, nf * sizeof(float), s->stream));
+    RtStats local{};
+    int rc = rt_render_device(s, rp, s->accum, s->stream, &local);
+    if (rc != RT_OK) return rc;
+    float spp = (float)(rp->spp_total ? rp->spp_total : (rp->sample_end - rp->sample_begin));
+    k_divide<<<(unsigned)((nf + 255) / 256), 256, 0, s->stream>>>(s->accum, nf, spp);
+    CU_TRY(cudaGetLastError());
+    CU_TRY(cudaMemcpyAsync(out_rgb_mean, s->accum, nf * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
+    CU_TRY(cudaStreamSynchronize(s->stream));
+    local.launches += 1;
+    local.ms_total = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count();
+    if (stats) *stats = local;
+    return RT_OK;
+}
+
+int rt_resolve_rgb8(RtScene* s, const float* rgb_mean, uint32_t width, uint32_t height, uint8_t* out_rgb8) {
+    if (!s || !rgb_mean || !out_rgb8 || width == 0 || height == 0) return fail(RT_ERR_ARG, "bad argument");
+    CU_TRY(cudaSetDevice(s->device));
+    size_t np = (size_t)width * height;
+    float* d_in = nullptr;
+    uint8_t* d_out = nullptr;
+    cudaError_t e;
+    if ((e = cudaMalloc(&d_in, np * 12)) != cudaSuccess || (e = cudaMalloc(&d_out, np * 3)) != cudaSuccess) {
+        cudaFree(d_in);
+        return fail(RT_ERR_CUDA, std::string("cudaMalloc: ") + cudaGetErrorString(e));
+    }
+    cudaMemcpyAsync(d_in, rgb_mean, np * 12, cudaMemcpyHostToDevice, s->stream);
+    k_resolve_rgb8<<<(unsigned)((np + 255) / 256), 256, 0, s->stream>>>(d_in, width, height, d_out);
+    cudaMemcpyAsync(out_rgb8, d_out, np * 3, cudaMemcpyDeviceToHost, s->stream);
+    e = cudaStreamSynchronize(s->stream);
+    cudaFree(d_in);
+    cudaFree(d_out);
+    if (e != cudaSuccess) return fail(RT_ERR_CUDA, std::string("resolve: ") + cudaGetErrorString(e));
+    return RT_OK;
+}
+
+int rt_measure_fp32_peak(int device, double* out_ffma_per_s, double* out_sm_mhz_effective) {
+    if (!out_ffma_per_s) return fail(RT_ERR_ARG, "NULL argument");
+    CU_TRY(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CU_TRY(cudaGetDeviceProperties(&prop, device));
+    float* d = nullptr;
+    CU_TRY(cudaMalloc(&d, 4));
+    cudaEvent_t e0, e1;
+    CU_TRY(cudaEventCreate(&e0));
+    CU_TRY(cudaEventCreate(&e1));
+    const int iters = 4096, blocks = prop.multiProcessorCount * 8, threads = 256;
+    double best = 0.0;
+    for (int rep = 0; rep < 5; rep++) {
+        cudaEventRecord(e0);
+        k_fp32_peak<<<blocks, threads>>>(d, iters, 1.0f);
+        cudaEventRecord(e1);
+        cudaError_t e = cudaEventSynchronize(e1);
+        if (e != cudaSuccess) {
+            cudaFree(d);
+            return fail(RT_ERR_CUDA, std::string("fp32 peak: ") + cudaGetErrorString(e));
+        }
+        float ms = 0.0f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        double ffma = (double)blocks * threads * iters * 16.0 * 8.0;
+        if (rep > 0) best = std::max(best, ffma / (ms * 1e-3));
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d);
+    *out_ffma_per_s = best;
+    if (out_sm_mhz_effective) *out_sm_mhz_effective = best / ((double)prop.multiProcessorCount * 128.0) / 1e6;
+    return RT_OK;
+}
+
+// ----------------------------------------------------------------------- test-only entry points
+// (declared in tests, not in rtgpu.h: parity of the shading / texture device code against the
+// oracle with identical injected random numbers)
+int rt_test_shade_cases(RtScene* s, const uint32_t* mat_ids, const float* rays, const float* recs, const float* xi,
+                        uint32_t xi_stride, uint32_t n, float* out) {
+    if (!s || !mat_ids || !rays || !recs || !xi || !out) return fail(RT_ERR_ARG, "NULL argument");
+    CU_TRY(cudaSetDevice(s->device));
+    uint32_t* d_m = nullptr;
+    float *d_r = nullptr, *d_c = nullptr, *d_x = nullptr, *d_o = nullptr;
+    CU_TRY(cudaMalloc(&d_m, n * 4));
+    CU_TRY(cudaMalloc(&d_r, (size_t)n * 24));
+    CU_TRY(cudaMalloc(&d_c, (size_t)n * 52));
+    CU_TRY(cudaMalloc(&d_x, (size_t)n * xi_stride * 4));
+    CU_TRY(cudaMalloc(&d_o, (size_t)n * 56));
+    cudaMemcpy(d_m, mat_ids, n * 4, cudaMemcpyHostToDevice);
+    cudaMemcpy(d_r, rays, (size_t)n * 24, cudaMemcpyHostToDevice);
+    cudaMemcpy(d_c, recs, (size_t)n * 52, cudaMemcpyHostToDevice);
+    cudaMemcpy(d_x, xi, (size_t)n * xi_stride * 4, cudaMemcpyHostToDevice);
+    k_shade_cases<<<(n + 63) / 64, 64, 0, s->stream>>>(s->ds, d_m, d_r, d_c, d_x, xi_stride, n, d_o);
+    cudaError_t e = cudaStreamSynchronize(s->stream);
+    cudaMemcpy(out, d_o, (size_t)n * 56, cudaMemcpyDeviceToHost);
+    cudaFree(d_m); cudaFree(d_r); cudaFree(d_c); cudaFree(d_x); cudaFree(d_o);
+    if (e != cudaSuccess) return fail(RT_ERR_CUDA, std::string("shade cases: ") + cudaGetErrorString(e));
+    return RT_OK;
+}
+
+int rt_test_texture_cases(RtScene* s, uint32_t tex, const float* uv, const float* p, uint32_t n, float* out) {
+    if (!s || !uv || !p || !out) return fail(RT_ERR_ARG, "NULL argument");
+    CU_TRY(cudaSetDevice(s->device));
+    float *d_uv = nullptr, *d_p = nullptr, *d_o = nullptr;
+    CU_TRY(cudaMalloc(&d_uv, (size_t)n * 8));
+    CU_TRY(cudaMalloc(&d_p, (size_t)n * 12));
+    CU_TRY(cudaMalloc(&d_o, (size_t)n * 12));
+    cudaMemcpy(d_uv, uv, (size_t)n * 8, cudaMemcpyHostToDevice);
+    cudaMemcpy(d_p, p, (size_t)n * 12, cudaMemcpyHostToDevice);
+    k_texture_cases<<<(n + 127) / 128, 128, 0, s->stream>>>(s->ds, tex, d_uv, d_p, n, d_o);
+    cudaError_t e = cudaStreamSynchronize(s->stream);
+    cudaMemcpy(out, d_o, (size_t)n * 12, cudaMemcpyDeviceToHost);
+    cudaFree(d_uv); cudaFree(d_p); cudaFree(d_o);
+    if (e != cudaSuccess) return fail(RT_ERR_CUDA, std::string("texture cases: ") + cudaGetErrorString(e));
+    return RT_OK;
+}
+
+// ------------------------------------------------------------------------- host scene builders
+struct RtHostScene {
+    std::unique_ptr<FlatSceneOwner> own;
+};
+
+int rt_host_scene_build(const char* name, float aspect_ratio, const char* asset_dir, RtHostScene** out) {
+    if (!name || !out) return fail(RT_ERR_ARG, "NULL argument");
+    *out = nullptr;
+    try {
+        std::unique_ptr<RtHostScene> hs(new RtHostScene());
+        hs->own = build_named_scene(name, aspect_ratio, asset_dir ? asset_dir : ".");
+        *out = hs.release();
+        return RT_OK;
+    } catch (const std::exception& e) {
+        std::string msg = e.what();
+        return fail(msg.find("cannot open") != std::string::npos || msg.find("PPM") != std::string::npos ? RT_ERR_IO : RT_ERR_ARG, msg);
+    }
+}
+const RtFlatScene* rt_host_scene_flat(const RtHostScene* hs) { return hs ? &hs->own->flat : nullptr; }
+void rt_host_scene_destroy(RtHostScene* hs) { delete hs; }
+
+}  // extern "C"
