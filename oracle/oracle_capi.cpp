@@ -183,23 +183,27 @@ int orc_closest_hit(OrcScene* s, const float* o, const float* d, const float* ti
 // generated before any is traced, c = sum / spp.  Output: linear mean RGB (before powf(0.5)),
 // pixel (i,j) at (j*nx+i)*3, j = 0 is the bottom row.  nthreads <= 0 -> all logical cores
 // (threadpool::Builder::new().build() default, src/main.rs:73).
-// column_begin/column_end bound the jobs (a bounded sample of the frame for timing).
+// column_begin/column_end/column_stride bound the jobs (a bounded, strided sample of the frame's
+// columns for timing; stride 1 = every column).
 int orc_render(OrcScene* s, uint32_t nx, uint32_t ny, uint32_t spp, int max_depth, int nthreads, uint64_t seed_base,
-               uint32_t column_begin, uint32_t column_end, float* out_mean, OrcStats* stats) {
+               uint32_t column_begin, uint32_t column_end, uint32_t column_stride, float* out_mean, OrcStats* stats) {
     if (!s || !out_mean) return -1;
     if (nthreads <= 0) nthreads = (int)std::thread::hardware_concurrency();
     if (nthreads <= 0) nthreads = 1;
     if (column_end > nx) column_end = nx;
+    if (column_stride == 0) column_stride = 1;
     const Scene& sc = *s->sc;
-    std::atomic<uint32_t> next{column_begin};
+    const uint32_t n_jobs = column_end > column_begin ? (column_end - column_begin + column_stride - 1) / column_stride : 0;
+    std::atomic<uint32_t> next{0};
     std::atomic<uint64_t> a_rays{0}, a_box{0}, a_prim{0}, a_shade{0}, a_viol{0};
     auto t0 = std::chrono::steady_clock::now();
     auto worker = [&]() {
         Counters& c = CNT();
         c = Counters();
         while (true) {
-            uint32_t i = next.fetch_add(1);
-            if (i >= column_end) break;
+            uint32_t job = next.fetch_add(1);
+            if (job >= n_jobs) break;
+            const uint32_t i = column_begin + job * column_stride;
             RNG() = SmallRng::seed_from_u64(seed_base + (uint64_t)i);
             std::vector<Ray> rays;
             rays.reserve(spp);
@@ -230,7 +234,7 @@ int orc_render(OrcScene* s, uint32_t nx, uint32_t ny, uint32_t spp, int max_dept
     for (auto& t : th) t.join();
     auto t1 = std::chrono::steady_clock::now();
     if (stats) {
-        stats->paths = (uint64_t)(column_end - column_begin) * ny * spp;
+        stats->paths = (uint64_t)n_jobs * ny * spp;
         stats->rays = a_rays;
         stats->box_tests = a_box;
         stats->prim_tests = a_prim;

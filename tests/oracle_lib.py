@@ -58,7 +58,7 @@ def lib() -> C.CDLL:
         L.orc_scene_free.restype = None
         L.orc_closest_hit.argtypes = [vp, vp, vp, vp, C.c_size_t, C.c_float, C.c_float, C.c_int, vp]
         L.orc_render.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_uint64, C.c_uint32,
-                                 C.c_uint32, vp, C.POINTER(OrcStats)]
+                                 C.c_uint32, C.c_uint32, vp, C.POINTER(OrcStats)]
         L.orc_resolve_rgb8.argtypes = [vp, C.c_uint32, C.c_uint32, vp]
         L.orc_resolve_rgb8.restype = None
         L.orc_scatter.argtypes = [vp, C.c_uint32, vp, vp, vp, vp, C.c_size_t, vp, C.POINTER(C.c_uint32)]
@@ -130,12 +130,13 @@ class OracleScene:
         assert rc == 0
         return out
 
-    def render(self, width, height, spp, max_depth=50, threads=0, seed_base=95, column_begin=0, column_end=None):
+    def render(self, width, height, spp, max_depth=50, threads=0, seed_base=95, column_begin=0, column_end=None,
+               column_stride=1):
         out = np.zeros((height, width, 3), np.float32)
         st = OrcStats()
         ce = width if column_end is None else column_end
-        rc = lib().orc_render(self.h, width, height, spp, max_depth, threads, seed_base, column_begin, ce, _p(out),
-                              C.byref(st))
+        rc = lib().orc_render(self.h, width, height, spp, max_depth, threads, seed_base, column_begin, ce, column_stride,
+                              _p(out), C.byref(st))
         assert rc == 0
         return out, st
 

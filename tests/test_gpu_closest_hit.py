@@ -56,12 +56,18 @@ def test_primary_hits_match_oracle(rtlib, oracle, name, w, h):
     assert np.array_equal(got["front_face"][hit], want["front_face"][hit])
     np.testing.assert_allclose(got["uv"][hit], want["uv"][hit], rtol=0, atol=2e-6)
 
-    # the reference's own BvhNode traversal (nested graph) vs its list semantics: report culling artefacts
+    # The reference's own BvhNode traversal (nested graph) vs its list semantics.  They can differ in two
+    # documented ways: (a) exact ties — AABB::hit rejects on `t_max <= t_min`
+    # (math.rs:108), so a later primitive whose box BEGINS exactly at the current closest t is culled and
+    # the earlier one keeps the hit (same t/p/n, other id; e.g. coplanar shared faces of adjacent GBoxes in
+    # final_scene); (b) grazing hits culled by the slab test.  Only (b) changes the geometry of the hit.
     nested = oracle.OracleScene.builtin(name, w / h)
     via_bvh = nested.closest_hit(o, d, times=times)
-    n_diff = int(np.count_nonzero(via_bvh["prim"] != want["prim"]))
-    print(f"{name}: {n} rays, {int(hit.sum())} hits, oracle ref-bvh vs list id differences: {n_diff}")
-    assert n_diff <= max(2, n // 20000)
+    id_diff = via_bvh["prim"] != want["prim"]
+    t_diff = via_bvh["t"].view(np.uint32) != want["t"].view(np.uint32)
+    print(f"{name}: {n} rays, {int(hit.sum())} hits; oracle ref-bvh vs list: {int(id_diff.sum())} id differences, "
+          f"of which {int((id_diff & ~t_diff).sum())} exact ties and {int((id_diff & t_diff).sum())} culling artefacts")
+    assert int(t_diff.sum()) <= max(2, n // 20000)
     scene.close()
 
 
