@@ -186,7 +186,11 @@ def run_ours(args, rank, world, local_rank):
     accum = torch.zeros(H * W * 3, dtype=torch.float32, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     host_out = torch.empty(H * W * 3, dtype=torch.float32).pin_memory()
-    stream = torch.cuda.current_stream(dev)
+    # one explicit (non-default) stream carries torch's ops, our kernels and the timing events alike
+    stream = torch.cuda.Stream(dev)
+    torch.cuda.synchronize(dev)
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
     params = scene.make_params(W, H, SPP, sample_begin=rank * SPP, sample_end=(rank + 1) * SPP, spp_total=spp_total,
                                max_depth=MAX_DEPTH, seed=95, mode=args.mode)
 

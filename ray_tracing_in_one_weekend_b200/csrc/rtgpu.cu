@@ -597,6 +597,62 @@ int rt_test_texture_cases(RtScene* s, uint32_t tex, const float* uv, const float
     return RT_OK;
 }
 
+// Host-only (no GPU): build the BVH of a flat scene and check its structural invariants —
+// every world primitive is referenced by exactly one leaf, child counts/encodings are sane, and
+// every child box encloses the boxes/leaves below it.  Returns 0 when valid.
+int rt_test_bvh_validate(const RtFlatScene* desc, uint32_t leaf_max, RtBvhInfo* info) {
+    std::string why = validate(desc);
+    if (!why.empty()) return fail(RT_ERR_ARG, why);
+    BvhBuildResult bvh;
+    try {
+        build_bvh4(*desc, leaf_max, bvh);
+    } catch (const std::exception& e) {
+        return fail(RT_ERR_ARG, e.what());
+    }
+    std::vector<int> seen(desc->n_prims, 0);
+    struct B { float lo[3], hi[3]; };
+    std::vector<B> node_box(bvh.nodes.size());
+    // bottom-up: children always have larger indices than their parent (pre-order emission)
+    for (int n = (int)bvh.nodes.size() - 1; n >= 0; n--) {
+        const BvhNode4& nd = bvh.nodes[n];
+        B acc{{INFINITY, INFINITY, INFINITY}, {-INFINITY, -INFINITY, -INFINITY}};
+        uint32_t nk = nd.pad[0];
+        if (nk < 1 || nk > 4) return fail(RT_ERR_ARG, "bvh: bad child count");
+        for (uint32_t k = 0; k < nk; k++) {
+            B cb{{nd.lox[k], nd.loy[k], nd.loz[k]}, {nd.hix[k], nd.hiy[k], nd.hiz[k]}};
+            uint32_t c = nd.child[k];
+            if (c & LEAF_FLAG) {
+                uint32_t first = c & LEAF_FIRST_MASK, cnt = ((c >> LEAF_COUNT_SHIFT) & 0xfu) + 1u;
+                if (first + cnt > bvh.leaf_order.size() || cnt > leaf_max) return fail(RT_ERR_ARG, "bvh: bad leaf range");
+                for (uint32_t i = 0; i < cnt; i++) {
+                    uint32_t flat = bvh.leaf_order[first + i];
+                    seen[flat]++;
+                    const RtPrim& p = desc->prims[flat];
+                    if (p.xform == 0 && (p.kind == RT_PRIM_SPHERE)) {  // untransformed spheres: exact containment check
+                        for (int a = 0; a < 3; a++)
+                            if (p.g[a] - p.g[3] < cb.lo[a] || p.g[a] + p.g[3] > cb.hi[a]) return fail(RT_ERR_ARG, "bvh: sphere outside its leaf box");
+                    }
+                }
+            } else {
+                if (c <= (uint32_t)n || c >= bvh.nodes.size()) return fail(RT_ERR_ARG, "bvh: bad child index");
+                for (int a = 0; a < 3; a++)
+                    if (node_box[c].lo[a] < cb.lo[a] || node_box[c].hi[a] > cb.hi[a]) return fail(RT_ERR_ARG, "bvh: child box not enclosed");
+            }
+            for (int a = 0; a < 3; a++) {
+                acc.lo[a] = std::fmin(acc.lo[a], cb.lo[a]);
+                acc.hi[a] = std::fmax(acc.hi[a], cb.hi[a]);
+            }
+        }
+        node_box[n] = acc;
+    }
+    for (uint32_t i = 0; i < desc->n_prims; i++) {
+        int want = (desc->prims[i].flags & RT_PRIM_FLAG_BOUNDARY_ONLY) ? 0 : 1;
+        if (seen[i] != want) return fail(RT_ERR_ARG, "bvh: primitive referenced " + std::to_string(seen[i]) + " times");
+    }
+    if (info) *info = RtBvhInfo{(uint32_t)bvh.nodes.size(), bvh.n_world_prims, bvh.max_depth, bvh.max_leaf_prims, bvh.sah_cost, (uint32_t)sizeof(BvhNode4)};
+    return RT_OK;
+}
+
 // ------------------------------------------------------------------------- host scene builders
 struct RtHostScene {
     std::unique_ptr<FlatSceneOwner> own;

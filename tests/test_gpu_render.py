@@ -43,8 +43,17 @@ def test_render_matches_oracle(rtlib, oracle, name, w, h, spp, tol):
     b, _ = ref.render(w, h, spp, seed_base=100095)
     assert st.paths == w * h * spp
     rel = abs(lum(img) - lum(a)) / lum(a)
-    noise = np.sqrt(np.nanmean((a - b) ** 2, axis=(0, 1)))
-    rmse = np.sqrt(np.nanmean((img - a) ** 2, axis=(0, 1)))
+    # The pbr.rs estimators (uniform-hemisphere sampling of peaked lobes) are heavy-tailed: a handful of
+    # firefly pixels dominates a plain RMSE and its own seed-to-seed spread.  RMSE is therefore taken on
+    # images clipped at the oracle image's 99.5th percentile (a no-op for the well-behaved scenes); the
+    # mean-luminance check above stays unclipped.  NaN pixels (the reference has no NaN filter, main.rs:98-105)
+    # are excluded and their count is compared instead.
+    cap = float(np.nanpercentile(a, 99.5))
+    ca, cb, ci = np.clip(a, 0, cap), np.clip(b, 0, cap), np.clip(img, 0, cap)
+    noise = np.sqrt(np.nanmean((ca - cb) ** 2, axis=(0, 1)))
+    rmse = np.sqrt(np.nanmean((ci - ca) ** 2, axis=(0, 1)))
+    nan_gpu, nan_cpu = int(np.isnan(img).any(-1).sum()), int(np.isnan(a).any(-1).sum())
+    assert abs(nan_gpu - nan_cpu) <= 3 + 0.5 * max(nan_gpu, nan_cpu), (nan_gpu, nan_cpu)
     rpp_gpu, rpp_cpu = st.rays / st.paths, sa.rays / sa.paths
     print(f"{name}: lum gpu {lum(img):.5f} cpu {lum(a):.5f} rel {rel:.4%}; rmse {rmse} noise floor {noise}; "
           f"rays/path gpu {rpp_gpu:.3f} cpu {rpp_cpu:.3f}; mean gpu {img.mean((0,1))} cpu {a.mean((0,1))}")

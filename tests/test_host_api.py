@@ -1,0 +1,109 @@
+"""Host-side logic, no GPU: the C-ABI library loads and exports every symbol of include/rtgpu.h, the host
+scene API re-expresses src/demo_scene.rs bit-identically to the oracle's restatement, the BVH builder's
+structural invariants hold, argument errors come back as negative codes (never aborts)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+SCENES = ["test_sphere", "sphere_scene", "textured", "cover_defocus", "cover_4k_motion", "simple_light_scene",
+          "cornell_box", "cornell_box_solid", "final_scene", "pbr_ibl", "furnace_diffuse", "furnace_disney_metal"]
+
+
+def test_library_exports_every_header_symbol(rtlib):
+    lib = rtlib.load_library()
+    header = open(os.path.join(os.path.dirname(rtlib.api.HERE), "include", "rtgpu.h")).read()
+    declared = set(re.findall(r"\b(rt_[a-z0-9_]+)\s*\(", header))
+    assert declared == set(rtlib.EXPORTED_SYMBOLS), declared ^ set(rtlib.EXPORTED_SYMBOLS)
+    for sym in declared:
+        assert getattr(lib, sym) is not None
+
+
+def test_struct_layouts_match_header(rtlib):
+    api = rtlib.api
+    assert C.sizeof(api.RtPrim) == 80 and C.sizeof(api.RtMaterial) == 32 and C.sizeof(api.RtTexture) == 32
+    assert C.sizeof(api.RtHit) == 44 and C.sizeof(api.RtPerlin) == 4096 + 768
+    assert C.sizeof(api.RtXformOp) == 16 and C.sizeof(api.RtXformChain) == 8
+
+
+@pytest.mark.parametrize("name", SCENES)
+def test_host_scene_equals_oracle_restatement(rtlib, oracle, name):
+    """Product flattener output == oracle flattener output, byte for byte (prims in the reference's
+    visitation order incl. BvhNode::new's RNG-driven sorts, transforms, materials, textures, Perlin tables,
+    decoded images, sky, camera)."""
+    hs = rtlib.HostScene(name, 1.5)
+    a = rtlib.flat_to_numpy(hs.flat)
+    ref = oracle.OracleScene.builtin(name, 1.5)
+    b = rtlib.flat_to_numpy(ref.flat)
+    for k in a:
+        if k == "images":
+            assert len(a[k]) == len(b[k]) and all(np.array_equal(x, y) for x, y in zip(a[k], b[k]))
+        else:
+            assert np.array_equal(a[k], b[k]), k
+
+
+def test_cover_100k_motion_scene_shape(rtlib):
+    hs = rtlib.HostScene("cover_100k_motion", 16 / 9)
+    f = hs.flat.contents
+    assert f.n_prims == 4 + 316 * 316
+    kinds = np.array([f.prims[i].kind for i in range(0, f.n_prims, 97)])
+    assert (kinds == 4).mean() > 0.7      # ~80 % moving Diffuse spheres
+    assert f.camera.time0 == 0.0 and f.camera.time1 == 1.0
+
+
+@pytest.mark.parametrize("name", ["test_sphere", "sphere_scene", "cornell_box", "final_scene", "cover_4k_motion", "pbr_ibl"])
+@pytest.mark.parametrize("leaf_max", [1, 4, 8])
+def test_bvh_invariants(rtlib, name, leaf_max):
+    lib = rtlib.load_library()
+    hs = rtlib.HostScene(name, 1.5)
+    info = rtlib.api.RtBvhInfo()
+    lib.rt_test_bvh_validate.argtypes = [C.POINTER(rtlib.RtFlatScene), C.c_uint32, C.POINTER(rtlib.api.RtBvhInfo)]
+    rc = lib.rt_test_bvh_validate(hs.flat, leaf_max, C.byref(info))
+    assert rc == 0, lib.rt_last_error()
+    assert info.node_bytes == 128 and info.max_leaf_prims <= leaf_max and info.n_nodes >= 1
+    assert info.max_depth * 3 + 4 <= 64
+
+
+def test_errors_are_codes_not_aborts(rtlib):
+    lib = rtlib.load_library()
+    h = C.c_void_p()
+    assert lib.rt_host_scene_build(b"no_such_scene", C.c_float(1.0), b"assets", C.byref(h)) == -1
+    assert b"unknown scene" in lib.rt_last_error()
+    assert lib.rt_host_scene_build(b"sphere_scene", C.c_float(1.0), b"/nonexistent", C.byref(h)) == -3
+    # malformed flat scenes
+    fs = rtlib.RtFlatScene()
+    out = C.c_void_p()
+    assert lib.rt_scene_create(C.byref(fs), 0, C.byref(out)) == -1          # abi_version 0
+    assert lib.rt_scene_create(None, 0, C.byref(out)) == -1
+    hs = rtlib.HostScene("test_sphere", 2.0)
+    bad = rtlib.RtFlatScene.from_buffer_copy(bytes(hs.flat.contents))
+    prims = (rtlib.api.RtPrim * 2)()
+    C.memmove(prims, hs.flat.contents.prims, C.sizeof(prims))
+    prims[1].mat = 99
+    bad.prims = prims
+    assert lib.rt_scene_create(C.byref(bad), 0, C.byref(out)) == -1
+    assert b"material" in lib.rt_last_error()
+    assert lib.rt_render(None, None, None, None) == -1
+
+
+def test_no_cpu_fallback_without_gpu(rtlib):
+    """On a box without a CUDA device the product path must fail loudly (RT_ERR_CUDA), not fall back."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    hs = rtlib.HostScene("test_sphere", 2.0)
+    with pytest.raises(rtlib.RtError) as e:
+        rtlib.Scene(hs.flat, 0)
+    assert e.value.code == -2
+
+
+def test_product_does_not_route_through_the_oracle():
+    """No file of the product package mentions the oracle library or imports the oracle wrapper."""
+    root = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "ray_tracing_in_one_weekend_b200")
+    for dp, _, files in os.walk(root):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".h")):
+                txt = open(os.path.join(dp, f), errors="replace").read()
+                assert "liboracle" not in txt and "oracle_lib" not in txt and "orc_" not in txt, f
