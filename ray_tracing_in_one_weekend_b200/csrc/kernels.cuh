@@ -19,7 +19,7 @@ __global__ void __launch_bounds__(128) k_closest_hit_batch(DeviceScene sc, const
     r.tm = times ? times[i] : 0.0f;
     PcgRng rng;
     rng.state = 0;
-    ClosestHit h = closest_hit<false>(sc, r, t_min, t_max, rng, /*skip_media=*/true, nullptr);
+    ClosestHit h = closest_hit<F_ALL, false>(sc, r, t_min, t_max, rng, /*skip_media=*/true, nullptr);
     RtHit o;
     if (h.prim == 0xffffffffu) {
         o.prim = -1;
@@ -29,7 +29,7 @@ __global__ void __launch_bounds__(128) k_closest_hit_batch(DeviceScene sc, const
         o.uv[0] = o.uv[1] = 0.0f;
         o.front_face = 0;
     } else {
-        HitRec rec = fill_hit(sc, r, h.prim, h.t, true);
+        HitRec rec = fill_hit<F_ALL>(sc, r, h.prim, h.t, true);
         o.prim = (int32_t)h.flat;
         o.t = rec.t;
         o.p[0] = rec.p.x; o.p[1] = rec.p.y; o.p[2] = rec.p.z;
@@ -66,7 +66,7 @@ RT_DEV unsigned long long warp_sum_u64(unsigned long long v) {
     return v;
 }
 
-template <bool COUNT>
+template <uint32_t F, bool COUNT>
 __global__ void __launch_bounds__(MEGA_THREADS) k_render_mega(DeviceScene sc, RenderArgs a) {
     const uint32_t lane = threadIdx.x & 31u;
     unsigned long long n_rays = 0, n_shade = 0;
@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(MEGA_THREADS) k_render_mega(DeviceScene sc, Re
                     alive = false;
                 } else {
                     n_rays++;
-                    ClosestHit h = closest_hit<COUNT>(sc, ray, 1e-3f, 3.402823466e+38f, rng, false, &tc);
+                    ClosestHit h = closest_hit<F, COUNT>(sc, ray, 1e-3f, 3.402823466e+38f, rng, false, &tc);
                     if (h.prim == 0xffffffffu) {
                         sum = sum + beta * sky_color(sc, ray.d);  // main.rs:58
                         alive = false;
@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(MEGA_THREADS) k_render_mega(DeviceScene sc, Re
                         n_shade++;
                         DevPrim hp = load_prim(sc.prims, h.prim);
                         DevMaterial m = load_mat(sc, hp.mat);
-                        HitRec rec = fill_hit(sc, ray, h.prim, h.t, (m.reserved & 1u) != 0u);
+                        HitRec rec = fill_hit<F>(sc, ray, h.prim, h.t, (m.reserved & 1u) != 0u);
                         V3f emitted, att;
                         Ray scattered;
                         bool ok = shade(sc, m, ray, rec, rng, emitted, att, scattered);
@@ -162,6 +162,230 @@ __global__ void __launch_bounds__(MEGA_THREADS) k_render_mega(DeviceScene sc, Re
             atomicAdd(a.stats + 4, pt);
         }
     }
+}
+
+// ======================================================================================= wavefront
+// Wavefront path tracer: a pool of P path slots lives in device memory (SoA, 64 B per path, sized to
+// stay L2-resident); every iteration advances every live path by one ray with two kernels:
+//
+//   k_wf_traverse<F>  one closest-hit query per live slot (small kernel: spheres-only variant has no
+//                     transform/medium/rect code), then classifies the result by SHADING CLASS (miss,
+//                     per material/texture group) and appends the slot id to that class's queue with a
+//                     warp-aggregated atomic (__match_any_sync + popc prefix: one atomicAdd per warp per class)
+//   k_wf_shade<F>     blockIdx.y = shading class: warps run ONE material group (material-sorted shading);
+//                     evaluates sky / emitted / scatter, accumulates radiance, writes the scattered ray
+//                     back into the slot, and REGENERATES a fresh camera path in place when the path died
+//                     (so the pool stays full and no compaction pass is needed until the frame drains).
+//
+// Replaces main.rs:38-60,84-97 exactly like the megakernel (same device functions, same RNG streams:
+// a path's stream depends only on (seed, pixel, global sample index)).
+constexpr int WF_NCLASS = 8;      // 0 miss | 1 diffuse const | 2 metal | 3 dielectric | 4 perlin-textured | 5 other classic | 6 pbr | 7 (total)
+constexpr int WF_TRAV_THREADS = 256;
+constexpr int WF_SHADE_THREADS = 128;
+
+struct WfArgs {
+    float4* ray_o;   // o.xyz, time
+    float4* ray_d;   // d.xyz, bits(depth | alive << 31)
+    float4* beta;    // throughput rgb, bits(pixel)
+    uint2* rng;      // PCG state
+    uint2* hit;      // bits(t), device prim (0xffffffff = miss)
+    uint32_t* queue; // WF_NCLASS-1 segments of P slot ids
+    uint32_t* n_class;  // [2][WF_NCLASS] double-buffered per-class counts; [.][7] = live slots traced
+    unsigned long long* path_counter;
+    unsigned long long* stats;  // [0] rays [1] shade calls [2..4] counters
+    float* accum;
+    uint32_t P;
+    uint32_t width, height;
+    uint32_t s_begin, n_samples, max_depth;
+    uint64_t seed;
+    unsigned long long total_paths;  // width * height * n_samples
+};
+
+constexpr uint32_t WF_ALIVE = 0x80000000u;
+
+// New camera path for a slot (main.rs:88-93).  Path index k -> (sample, pixel): k = s * (W*H) + pixel, pixels
+// row-major, so the 32 lanes of a warp start on 32 neighbouring pixels of one row with the same sample index.
+RT_DEV void wf_generate(const DeviceScene& sc, const WfArgs& a, unsigned long long k, Ray& ray, V3f& beta, uint32_t& pixel,
+                        PcgRng& rng) {
+    const unsigned long long per_sample = (unsigned long long)a.width * a.height;
+    const uint32_t s = a.s_begin + (uint32_t)(k / per_sample);
+    pixel = (uint32_t)(k % per_sample);
+    const uint32_t py = pixel / a.width, px = pixel - py * a.width;
+    rng.seed(a.seed, pixel, s);
+    float u = ((float)px + rng.next()) / (float)a.width;
+    float v = ((float)py + rng.next()) / (float)a.height;
+    ray = camera_get_ray(sc.cam, u, v, rng);
+    beta = mk3(1.0f, 1.0f, 1.0f);
+}
+
+// Warp-aggregated fetch of new path indices for the lanes with `want` set. Returns k (or ~0 when none left).
+RT_DEV unsigned long long wf_fetch(const WfArgs& a, bool want) {
+    const uint32_t mask = __ballot_sync(0xffffffffu, want);
+    if (mask == 0) return ~0ull;
+    const uint32_t lane = threadIdx.x & 31u;
+    const int leader = __ffs(mask) - 1;
+    unsigned long long base = 0;
+    if ((int)lane == leader) base = atomicAdd(a.path_counter, (unsigned long long)__popc(mask));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return want ? base + (unsigned long long)__popc(mask & ((1u << lane) - 1u)) : ~0ull;
+}
+
+RT_DEV void wf_store_path(const WfArgs& a, uint32_t slot, const Ray& ray, V3f beta, uint32_t pixel, uint32_t depth, bool alive,
+                          const PcgRng& rng) {
+    a.ray_o[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.tm);
+    a.ray_d[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(depth | (alive ? WF_ALIVE : 0u)));
+    a.beta[slot] = make_float4(beta.x, beta.y, beta.z, __uint_as_float(pixel));
+    a.rng[slot] = make_uint2((uint32_t)rng.state, (uint32_t)(rng.state >> 32));
+}
+
+// Fill slots with fresh camera paths (frame start).
+__global__ void __launch_bounds__(256) k_wf_generate(DeviceScene sc, WfArgs a) {
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;  // P is a multiple of 256
+    Ray ray;
+    ray.o = ray.d = mk3(0.0f, 0.0f, 0.0f);
+    ray.tm = 0.0f;
+    V3f beta = mk3(1.0f, 1.0f, 1.0f);
+    uint32_t pixel = 0;
+    PcgRng rng;
+    rng.state = 0;
+    bool alive = false;
+    unsigned long long k = wf_fetch(a, true);
+    if (k < a.total_paths) {
+        wf_generate(sc, a, k, ray, beta, pixel, rng);
+        alive = true;
+    }
+    wf_store_path(a, slot, ray, beta, pixel, 0u, alive, rng);
+}
+
+template <uint32_t F, bool COUNT>
+__global__ void __launch_bounds__(WF_TRAV_THREADS) k_wf_traverse(DeviceScene sc, WfArgs a, int buf) {
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;  // P is a multiple of the block size
+    const uint32_t lane = threadIdx.x & 31u;
+    const float4 rd = a.ray_d[slot];
+    const bool alive = (__float_as_uint(rd.w) & WF_ALIVE) != 0u;
+    uint32_t cls = 0xffu;
+    TravCounters tc;
+    if (alive) {
+        const float4 ro = a.ray_o[slot];
+        Ray ray;
+        ray.o = mk3(ro.x, ro.y, ro.z);
+        ray.d = mk3(rd.x, rd.y, rd.z);
+        ray.tm = ro.w;
+        PcgRng rng;
+        rng.state = 0;
+        if (F & F_MEDIA) {
+            uint2 st = a.rng[slot];
+            rng.state = ((unsigned long long)st.y << 32) | st.x;
+        }
+        // main.rs:39: a non-unit direction loses the path; treat as a miss with zero throughput
+        ClosestHit h;
+        h.prim = 0xffffffffu;
+        h.t = 0.0f;
+        bool unit = vec3a_near_one(ray.d);
+        if (unit) h = closest_hit<F, COUNT>(sc, ray, 1e-3f, 3.402823466e+38f, rng, false, &tc);
+        if (F & F_MEDIA) a.rng[slot] = make_uint2((uint32_t)rng.state, (uint32_t)(rng.state >> 32));
+        if (!unit) {
+            float4 b = a.beta[slot];
+            a.beta[slot] = make_float4(0.0f, 0.0f, 0.0f, b.w);
+        }
+        a.hit[slot] = make_uint2(__float_as_uint(h.t), h.prim);
+        cls = 0u;
+        if (h.prim != 0xffffffffu) {
+            const uint32_t mat = __ldg(&sc.prims[h.prim].mat);
+            cls = (__ldg(&sc.mats[mat].reserved) >> 8) & 0xffu;
+        }
+    }
+    // ---- queue append: one atomicAdd per warp per class (ballot/match + popc prefix) ---------------
+    const uint32_t active = __ballot_sync(0xffffffffu, alive);
+    if (alive) {
+        const uint32_t peers = __match_any_sync(active, cls);
+        const int leader = __ffs(peers) - 1;
+        uint32_t base = 0;
+        if ((int)lane == leader) base = atomicAdd(a.n_class + buf * WF_NCLASS + cls, (uint32_t)__popc(peers));
+        base = __shfl_sync(peers, base, leader);
+        a.queue[(size_t)cls * a.P + base + __popc(peers & ((1u << lane) - 1u))] = slot;
+    }
+    if (lane == 0 && active) {
+        atomicAdd(a.n_class + buf * WF_NCLASS + 7, (uint32_t)__popc(active));
+        atomicAdd(a.stats + 0, (unsigned long long)__popc(active));
+    }
+    if (COUNT) {
+        unsigned long long nv = warp_sum_u64(tc.node_visits), bt = warp_sum_u64(tc.box_tests), pt = warp_sum_u64(tc.prim_tests);
+        if (lane == 0) {
+            atomicAdd(a.stats + 2, nv);
+            atomicAdd(a.stats + 3, bt);
+            atomicAdd(a.stats + 4, pt);
+        }
+    }
+}
+
+template <uint32_t F>
+__global__ void __launch_bounds__(WF_SHADE_THREADS) k_wf_shade(DeviceScene sc, WfArgs a, int buf) {
+    const uint32_t cls = blockIdx.y;
+    const uint32_t n = a.n_class[buf * WF_NCLASS + cls];
+    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x < WF_NCLASS) a.n_class[(buf ^ 1) * WF_NCLASS + threadIdx.x] = 0u;
+    const uint32_t n_round = (n + 31u) & ~31u;
+    unsigned long long n_shade = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
+        const bool active = i < n;
+        uint32_t slot = 0, pixel = 0, depth = 0;
+        Ray ray;
+        ray.o = ray.d = mk3(0.0f, 0.0f, 0.0f);
+        ray.tm = 0.0f;
+        V3f beta = mk3(0.0f, 0.0f, 0.0f);
+        PcgRng rng;
+        rng.state = 0;
+        bool alive = false;
+        if (active) {
+            slot = a.queue[(size_t)cls * a.P + i];
+            const float4 ro = a.ray_o[slot], rd = a.ray_d[slot], bt = a.beta[slot];
+            const uint2 st = a.rng[slot], ht = a.hit[slot];
+            ray.o = mk3(ro.x, ro.y, ro.z);
+            ray.d = mk3(rd.x, rd.y, rd.z);
+            ray.tm = ro.w;
+            depth = __float_as_uint(rd.w) & 0xffu;
+            beta = mk3(bt.x, bt.y, bt.z);
+            pixel = __float_as_uint(bt.w);
+            rng.state = ((unsigned long long)st.y << 32) | st.x;
+            V3f add = mk3(0.0f, 0.0f, 0.0f);
+            if (cls == 0u) {
+                // main.rs:58; a path dropped by the unit-direction check arrives here with beta == 0
+                if (beta.x != 0.0f || beta.y != 0.0f || beta.z != 0.0f) add = beta * sky_color(sc, ray.d);
+            } else {
+                n_shade++;
+                DevPrim hp = load_prim(sc.prims, ht.y);
+                DevMaterial m = load_mat(sc, hp.mat);
+                HitRec rec = fill_hit<F>(sc, ray, ht.y, __uint_as_float(ht.x), (m.reserved & 1u) != 0u);
+                V3f emitted, att;
+                Ray scattered;
+                bool ok = shade(sc, m, ray, rec, rng, emitted, att, scattered);
+                add = beta * emitted;  // main.rs:47
+                if (ok) {              // main.rs:48-54
+                    beta = beta * att;
+                    ray = scattered;
+                    depth++;
+                    alive = depth <= a.max_depth;  // main.rs:40-42
+                }
+            }
+            if (add.x != 0.0f || add.y != 0.0f || add.z != 0.0f) {
+                float* px_out = a.accum + (size_t)pixel * 3u;
+                atomicAdd(px_out + 0, add.x);
+                atomicAdd(px_out + 1, add.y);
+                atomicAdd(px_out + 2, add.z);
+            }
+        }
+        // ---- regenerate a fresh camera path in place when this one ended ---------------------------
+        const bool want = active && !alive;
+        const unsigned long long k = wf_fetch(a, want);
+        if (want && k < a.total_paths) {
+            wf_generate(sc, a, k, ray, beta, pixel, rng);
+            depth = 0;
+            alive = true;
+        }
+        if (active) wf_store_path(a, slot, ray, beta, pixel, depth, alive, rng);
+    }
+    n_shade = warp_sum_u64(n_shade);
+    if ((threadIdx.x & 31u) == 0 && n_shade) atomicAdd(a.stats + 1, n_shade);
 }
 
 // ------------------------------------------------------------------------------------- test kernels

@@ -43,6 +43,11 @@ struct RtScene {
     size_t accum_floats = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int mega_blocks_per_sm = 0, mega_blocks_per_sm_cnt = 0, sm_count = 0;
+    uint32_t features = 0;  // F_* bits present in the scene
+    // wavefront pool (allocated on first use)
+    WfArgs wf{};
+    std::vector<void*> wf_allocs;
+    uint32_t* wf_host_counts = nullptr;  // pinned
 
     ~RtScene() {
         cudaSetDevice(device);
@@ -50,6 +55,8 @@ struct RtScene {
         for (auto a : arrays) cudaFreeArray(a);
         for (auto p : allocs) cudaFree(p);
         if (accum) cudaFree(accum);
+        for (auto p : wf_allocs) cudaFree(p);
+        if (wf_host_counts) cudaFreeHost(wf_host_counts);
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
         if (stream) cudaStreamDestroy(stream);
@@ -122,6 +129,14 @@ std::string validate(const RtFlatScene* d) {
     if (d->sky.kind > RT_SKY_CONSTANT) return "bad sky kind";
     if (d->sky.kind == RT_SKY_ENVMAP && d->sky.image >= d->n_images) return "sky image out of range";
     return "";
+}
+
+// does texture i (transitively through checker children) contain a texture of `kind`?
+bool tex_uses_kind(const RtFlatScene* d, uint32_t i, uint32_t kind, int depth = 0) {
+    const RtTexture& t = d->textures[i];
+    if (t.kind == kind) return true;
+    if (t.kind == RT_TEX_CHECKER && depth < 8) return tex_uses_kind(d, t.a, kind, depth + 1) || tex_uses_kind(d, t.b, kind, depth + 1);
+    return false;
 }
 
 // does texture i (transitively) read uv?
@@ -241,6 +256,17 @@ int rt_scene_create(const RtFlatScene* desc, int device, RtScene** out) {
         uint32_t flags = 0;
         if (t0 && tex_needs_uv(desc, m.tex0)) flags |= 1u;
         if (m.kind == RT_MAT_ROUGH_PLASTIC && tex_needs_uv(desc, m.tex1)) flags |= 1u;
+        // shading class for the wavefront's material-sorted shade pass (kernels.cuh WF_NCLASS)
+        const bool perlin = (t0 && tex_uses_kind(desc, m.tex0, RT_TEX_PERLIN)) ||
+                            (m.kind == RT_MAT_ROUGH_PLASTIC && tex_uses_kind(desc, m.tex1, RT_TEX_PERLIN));
+        const bool const_tex = t0 && desc->textures[m.tex0].kind == RT_TEX_CONSTANT;
+        uint32_t cls = 5u;
+        if (perlin) cls = 4u;
+        else if (m.kind >= RT_MAT_OREN_NAYAR) cls = 6u;
+        else if (m.kind == RT_MAT_DIFFUSE && const_tex) cls = 1u;
+        else if (m.kind == RT_MAT_METAL) cls = 2u;
+        else if (m.kind == RT_MAT_DIELECTRIC) cls = 3u;
+        flags |= cls << 8;
         mats[i] = DevMaterial{m.kind, m.tex0, m.tex1, flags, m.p[0], m.p[1], m.p[2], m.p[3]};
     }
     std::vector<DevTexture> texs(desc->n_textures);
@@ -318,6 +344,13 @@ int rt_scene_create(const RtFlatScene* desc, int device, RtScene** out) {
     s->ds.n_world_prims = bvh.n_world_prims;
     s->ds.n_prims = (uint32_t)prims.size();
     s->ds.has_media = has_media ? 1u : 0u;
+    for (uint32_t i = 0; i < desc->n_prims; i++) {
+        const RtPrim& p = desc->prims[i];
+        if (p.xform != 0) s->features |= F_XFORM;
+        if (p.kind == RT_PRIM_MEDIUM) s->features |= F_MEDIA;
+        if (p.kind == RT_PRIM_MOVING_SPHERE) s->features |= F_MOTION;
+        if (p.kind == RT_PRIM_XYRECT || p.kind == RT_PRIM_XZRECT || p.kind == RT_PRIM_YZRECT) s->features |= F_RECT;
+    }
     s->camera = c;
     s->bvh = RtBvhInfo{(uint32_t)bvh.nodes.size(), bvh.n_world_prims, bvh.max_depth, bvh.max_leaf_prims, bvh.sah_cost, (uint32_t)sizeof(BvhNode4)};
     if (bvh.max_depth * 3u + 4u > (uint32_t)STACK_SIZE) return fail(RT_ERR_UNSUPPORTED, "BVH too deep for the traversal stack");
@@ -330,10 +363,13 @@ int rt_scene_create(const RtFlatScene* desc, int device, RtScene** out) {
     s->allocs.push_back(p);
     s->stats = (unsigned long long*)p;
     // the traversal stack lives in local memory: make sure L1 is preferred over shared memory
-    CU_TRY(cudaFuncSetAttribute(k_render_mega<false>, cudaFuncAttributePreferredSharedMemoryCarveout, 0));
-    CU_TRY(cudaFuncSetAttribute(k_render_mega<true>, cudaFuncAttributePreferredSharedMemoryCarveout, 0));
-    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->mega_blocks_per_sm, k_render_mega<false>, MEGA_THREADS, 0));
-    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->mega_blocks_per_sm_cnt, k_render_mega<true>, MEGA_THREADS, 0));
+    if (s->features == 0) {
+        CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->mega_blocks_per_sm, k_render_mega<0u, false>, MEGA_THREADS, 0));
+        CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->mega_blocks_per_sm_cnt, k_render_mega<0u, true>, MEGA_THREADS, 0));
+    } else {
+        CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->mega_blocks_per_sm, k_render_mega<F_ALL, false>, MEGA_THREADS, 0));
+        CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->mega_blocks_per_sm_cnt, k_render_mega<F_ALL, true>, MEGA_THREADS, 0));
+    }
     if (s->mega_blocks_per_sm < 1 || s->mega_blocks_per_sm_cnt < 1) return fail(RT_ERR_CUDA, "render kernel does not fit on an SM");
     CU_TRY(cudaDeviceSynchronize());
     *out = s.release();
@@ -403,10 +439,115 @@ int rt_camera_get_rays(const RtCamera* cam, const float* uv, size_t n, float* o_
     return RT_OK;
 }
 
+static int wf_ensure_pool(RtScene* s) {
+    if (s->wf.P) return RT_OK;
+    uint32_t P = (uint32_t)env_int("RT_WF_POOL", 1 << 20);
+    P = std::max(256u * 32u, (P + 8191u) & ~8191u);
+    auto alloc = [&](size_t bytes, void** out) -> cudaError_t {
+        cudaError_t e = cudaMalloc(out, bytes);
+        if (e == cudaSuccess) s->wf_allocs.push_back(*out);
+        return e;
+    };
+    CU_TRY(alloc((size_t)P * 16, (void**)&s->wf.ray_o));
+    CU_TRY(alloc((size_t)P * 16, (void**)&s->wf.ray_d));
+    CU_TRY(alloc((size_t)P * 16, (void**)&s->wf.beta));
+    CU_TRY(alloc((size_t)P * 8, (void**)&s->wf.rng));
+    CU_TRY(alloc((size_t)P * 8, (void**)&s->wf.hit));
+    CU_TRY(alloc((size_t)P * 4 * (WF_NCLASS - 1), (void**)&s->wf.queue));
+    CU_TRY(alloc(2 * WF_NCLASS * sizeof(uint32_t), (void**)&s->wf.n_class));
+    CU_TRY(alloc(sizeof(unsigned long long), (void**)&s->wf.path_counter));
+    CU_TRY(cudaMallocHost((void**)&s->wf_host_counts, 2 * WF_NCLASS * sizeof(uint32_t)));
+    s->wf.P = P;
+    return RT_OK;
+}
+
+// Wavefront frame: generate, then (traverse, shade) until the pool drains.  The loop needs the live count
+// on the host every few iterations, so this mode synchronises `st` internally.
+static int render_wavefront(RtScene* s, const RtRenderParams* rp, float* accum, cudaStream_t st, bool count, uint32_t* launches,
+                            uint32_t* iterations) {
+    int rc = wf_ensure_pool(s);
+    if (rc != RT_OK) return rc;
+    WfArgs a = s->wf;
+    a.stats = s->stats;
+    a.accum = accum;
+    a.width = rp->width;
+    a.height = rp->height;
+    a.s_begin = rp->sample_begin;
+    a.n_samples = rp->sample_end - rp->sample_begin;
+    a.max_depth = rp->max_depth;
+    a.seed = rp->seed;
+    a.total_paths = (unsigned long long)rp->width * rp->height * a.n_samples;
+    CU_TRY(cudaMemsetAsync(a.n_class, 0, 2 * WF_NCLASS * sizeof(uint32_t), st));
+    CU_TRY(cudaMemsetAsync(a.path_counter, 0, sizeof(unsigned long long), st));
+    const uint32_t P = a.P;
+    k_wf_generate<<<P / 256, 256, 0, st>>>(s->ds, a);
+    *launches = 1;
+    const dim3 shade_grid((unsigned)(s->sm_count * env_int("RT_WF_SHADE_BLOCKS", 4)), WF_NCLASS - 1);
+    const bool simple = s->features == 0;
+    const unsigned long long min_iters = a.total_paths / P;  // every path needs at least one ray
+    int buf = 0;
+    uint32_t it = 0;
+    for (;; it++) {
+        if (simple) {
+            if (count) k_wf_traverse<0u, true><<<P / WF_TRAV_THREADS, WF_TRAV_THREADS, 0, st>>>(s->ds, a, buf);
+            else k_wf_traverse<0u, false><<<P / WF_TRAV_THREADS, WF_TRAV_THREADS, 0, st>>>(s->ds, a, buf);
+            k_wf_shade<0u><<<shade_grid, WF_SHADE_THREADS, 0, st>>>(s->ds, a, buf);
+        } else {
+            if (count) k_wf_traverse<F_ALL, true><<<P / WF_TRAV_THREADS, WF_TRAV_THREADS, 0, st>>>(s->ds, a, buf);
+            else k_wf_traverse<F_ALL, false><<<P / WF_TRAV_THREADS, WF_TRAV_THREADS, 0, st>>>(s->ds, a, buf);
+            k_wf_shade<F_ALL><<<shade_grid, WF_SHADE_THREADS, 0, st>>>(s->ds, a, buf);
+        }
+        *launches += 2;
+        if (it >= min_iters && (it & 7u) == 7u) {
+            // n_class[buf][7] = number of live slots the last traverse saw (zeroed only by the NEXT shade)
+            CU_TRY(cudaMemcpyAsync(s->wf_host_counts, a.n_class, 2 * WF_NCLASS * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+            CU_TRY(cudaStreamSynchronize(st));
+            if (s->wf_host_counts[buf * WF_NCLASS + 7] == 0) break;
+        }
+        buf ^= 1;
+        if (it > 100000000u) return fail(RT_ERR_CUDA, "wavefront did not drain");
+    }
+    CU_TRY(cudaGetLastError());
+    *iterations = it + 1;
+    return RT_OK;
+}
+
 int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* cuda_stream, RtStats* stats) {
     if (!s || !rp || !accum) return fail(RT_ERR_ARG, "NULL argument");
     if (rp->width == 0 || rp->height == 0 || rp->sample_end < rp->sample_begin) return fail(RT_ERR_ARG, "bad render params");
-    if (rp->mode == RT_MODE_WAVEFRONT) return fail(RT_ERR_UNSUPPORTED, "wavefront mode not built yet");
+    if (rp->mode > RT_MODE_WAVEFRONT) return fail(RT_ERR_ARG, "bad render mode");
+    uint32_t mode = rp->mode;
+    if (mode == RT_MODE_AUTO) mode = (uint32_t)env_int("RT_DEFAULT_MODE", RT_MODE_MEGAKERNEL);
+    if (mode == RT_MODE_WAVEFRONT && rp->sample_end > rp->sample_begin) {
+        auto w0 = std::chrono::steady_clock::now();
+        CU_TRY(cudaSetDevice(s->device));
+        cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : s->stream;
+        CU_TRY(cudaMemsetAsync(s->stats, 0, 8 * sizeof(unsigned long long), st));
+        CU_TRY(cudaEventRecord(s->ev0, st));
+        uint32_t launches = 0, iters = 0;
+        int rc = render_wavefront(s, rp, accum, st, (rp->flags & RT_RENDER_COUNTERS) != 0, &launches, &iters);
+        if (rc != RT_OK) return rc;
+        CU_TRY(cudaEventRecord(s->ev1, st));
+        if (stats) {
+            std::memset(stats, 0, sizeof(*stats));
+            unsigned long long h[8] = {0};
+            CU_TRY(cudaMemcpyAsync(h, s->stats, sizeof(h), cudaMemcpyDeviceToHost, st));
+            CU_TRY(cudaStreamSynchronize(st));
+            float ms = 0.0f;
+            CU_TRY(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+            stats->ms_kernel = ms;
+            stats->paths = (uint64_t)rp->width * rp->height * (rp->sample_end - rp->sample_begin);
+            stats->rays = h[0];
+            stats->shade_calls = h[1];
+            stats->node_visits = h[2];
+            stats->box_tests = h[3];
+            stats->prim_tests = h[4];
+            stats->launches = launches;
+            stats->mode_used = RT_MODE_WAVEFRONT;
+            stats->ms_total = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - w0).count();
+        }
+        return RT_OK;
+    }
     auto wall0 = std::chrono::steady_clock::now();
     CU_TRY(cudaSetDevice(s->device));
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : s->stream;
@@ -440,10 +581,13 @@ int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* c
         CU_TRY(cudaMemsetAsync(s->work_counter, 0, sizeof(unsigned int), st));
         CU_TRY(cudaMemsetAsync(s->stats, 0, 8 * sizeof(unsigned long long), st));
         if (stats) CU_TRY(cudaEventRecord(s->ev0, st));
-        if (count)
-            k_render_mega<true><<<grid, MEGA_THREADS, 0, st>>>(s->ds, a);
-        else
-            k_render_mega<false><<<grid, MEGA_THREADS, 0, st>>>(s->ds, a);
+        if (s->features == 0) {
+            if (count) k_render_mega<0u, true><<<grid, MEGA_THREADS, 0, st>>>(s->ds, a);
+            else k_render_mega<0u, false><<<grid, MEGA_THREADS, 0, st>>>(s->ds, a);
+        } else {
+            if (count) k_render_mega<F_ALL, true><<<grid, MEGA_THREADS, 0, st>>>(s->ds, a);
+            else k_render_mega<F_ALL, false><<<grid, MEGA_THREADS, 0, st>>>(s->ds, a);
+        }
         CU_TRY(cudaGetLastError());
         launches = 1;
         if (stats) CU_TRY(cudaEventRecord(s->ev1, st));

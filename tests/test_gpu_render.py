@@ -32,15 +32,31 @@ CASES = [
 ]
 
 
+_ORACLE_CACHE = {}
+
+
+def _oracle_renders(oracle, hs, name, w, h, spp):
+    key = (name, w, h, spp)
+    if key not in _ORACLE_CACHE:
+        ref = oracle.OracleScene.from_flat(hs.flat)
+        a, sa = ref.render(w, h, spp, seed_base=95)
+        b, _ = ref.render(w, h, spp, seed_base=100095)
+        _ORACLE_CACHE[key] = (a, sa.rays / sa.paths, b)
+    return _ORACLE_CACHE[key]
+
+
+MODES = [pytest.param(1, id="megakernel"), pytest.param(2, id="wavefront")]
+
+
+@pytest.mark.parametrize("mode", MODES)
 @pytest.mark.parametrize("name,w,h,spp,tol", CASES)
-def test_render_matches_oracle(rtlib, oracle, name, w, h, spp, tol):
+def test_render_matches_oracle(rtlib, oracle, name, w, h, spp, tol, mode):
     rt = rtlib
     hs = rt.HostScene(name, w / h)
     scene = rt.Scene(hs.flat, 0)
-    ref = oracle.OracleScene.from_flat(hs.flat)
-    img, st = scene.render(w, h, spp)
-    a, sa = ref.render(w, h, spp, seed_base=95)
-    b, _ = ref.render(w, h, spp, seed_base=100095)
+    img, st = scene.render(w, h, spp, mode=mode)
+    assert st.mode_used == mode
+    a, rpp_cpu, b = _oracle_renders(oracle, hs, name, w, h, spp)
     assert st.paths == w * h * spp
     rel = abs(lum(img) - lum(a)) / lum(a)
     # The pbr.rs estimators (uniform-hemisphere sampling of peaked lobes) are heavy-tailed: a handful of
@@ -54,7 +70,7 @@ def test_render_matches_oracle(rtlib, oracle, name, w, h, spp, tol):
     rmse = np.sqrt(np.nanmean((ci - ca) ** 2, axis=(0, 1)))
     nan_gpu, nan_cpu = int(np.isnan(img).any(-1).sum()), int(np.isnan(a).any(-1).sum())
     assert abs(nan_gpu - nan_cpu) <= 3 + 0.5 * max(nan_gpu, nan_cpu), (nan_gpu, nan_cpu)
-    rpp_gpu, rpp_cpu = st.rays / st.paths, sa.rays / sa.paths
+    rpp_gpu = st.rays / st.paths
     print(f"{name}: lum gpu {lum(img):.5f} cpu {lum(a):.5f} rel {rel:.4%}; rmse {rmse} noise floor {noise}; "
           f"rays/path gpu {rpp_gpu:.3f} cpu {rpp_cpu:.3f}; mean gpu {img.mean((0,1))} cpu {a.mean((0,1))}")
     assert rel <= tol
@@ -63,30 +79,44 @@ def test_render_matches_oracle(rtlib, oracle, name, w, h, spp, tol):
     scene.close()
 
 
+@pytest.mark.parametrize("mode", MODES)
 @pytest.mark.parametrize("mat,expect", [("diffuse", (0.6, 0.5, 0.4)), ("lambert", (0.6, 0.5, 0.4)),
                                         ("metal", (0.6, 0.5, 0.4)), ("dielectric", (1.0, 1.0, 1.0))])
-def test_furnace(rtlib, mat, expect):
+def test_furnace(rtlib, mat, expect, mode):
     """K10: one convex sphere under a constant white sky — the centre pixel converges to the albedo
     (Diffuse weight rho; Lambert weight 2 rho cos on the uniform hemisphere; Metal rho; Dielectric 1)."""
     rt = rtlib
     scene = rt.Scene.from_name("furnace_" + mat, 1.0, 0)
-    img, _ = scene.render(9, 9, 8192)
+    img, _ = scene.render(9, 9, 8192, mode=mode)
     c = img[4, 4]
     np.testing.assert_allclose(c, expect, rtol=0.02)
     scene.close()
 
 
-def test_sample_partition_is_additive(rtlib):
+@pytest.mark.parametrize("mode", MODES)
+def test_sample_partition_is_additive(rtlib, mode):
     """Multi-GPU contract: rendering sample ranges [0,a) and [a,n) separately and summing equals the
     one-shot render of [0,n) up to float summation order (RNG streams keyed on the global sample index)."""
     import ctypes as C
     rt = rtlib
     w, h, n = 64, 48, 64
     scene = rt.Scene.from_name("sphere_scene", w / h, 0)
-    full, _ = scene.render(w, h, n)
-    p1, _ = scene.render(w, h, n, sample_begin=0, sample_end=24, spp_total=n)
-    p2, _ = scene.render(w, h, n, sample_begin=24, sample_end=n, spp_total=n)
+    full, _ = scene.render(w, h, n, mode=mode)
+    p1, _ = scene.render(w, h, n, sample_begin=0, sample_end=24, spp_total=n, mode=mode)
+    p2, _ = scene.render(w, h, n, sample_begin=24, sample_end=n, spp_total=n, mode=mode)
     np.testing.assert_allclose(p1 + p2, full, rtol=2e-5, atol=1e-6)
+    scene.close()
+
+
+def test_modes_agree_on_ray_statistics(rtlib):
+    """Megakernel and wavefront use the same per-path RNG streams -> identical ray counts and images up to
+    float summation order (atomics)."""
+    rt = rtlib
+    scene = rt.Scene.from_name("sphere_scene", 1.5, 0)
+    a, sa = scene.render(96, 64, 32, mode=1)
+    b, sb = scene.render(96, 64, 32, mode=2)
+    assert sa.rays == sb.rays and sa.shade_calls == sb.shade_calls
+    np.testing.assert_allclose(a, b, rtol=1e-4, atol=1e-5)
     scene.close()
 
 
