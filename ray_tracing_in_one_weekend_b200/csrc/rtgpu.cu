@@ -27,6 +27,9 @@ static int fail(int code, const std::string& msg) {
             return fail(RT_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e__));                 \
     } while (0)
 
+constexpr int WF_MAX_CHAINS = 8;
+constexpr int WF_GRAPH_ITERS = 8;  // wavefront iterations per graph launch (even: the count buffers alternate)
+
 struct RtScene {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -44,10 +47,16 @@ struct RtScene {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int mega_blocks_per_sm = 0, mega_blocks_per_sm_cnt = 0, sm_count = 0;
     uint32_t features = 0;  // F_* bits present in the scene
-    // wavefront pool (allocated on first use)
-    WfArgs wf{};
+    uint32_t class_mask = 0;  // shading classes (CLS_*) of the scene's materials
+    // wavefront pool + the CUDA graph of WF_GRAPH_ITERS iterations (built on first use)
+    WfArgs wf[WF_MAX_CHAINS]{};  // independent sub-pools ("chains") whose kernels overlap on the GPU
+    int wf_chains = 0;
     std::vector<void*> wf_allocs;
     uint32_t* wf_host_counts = nullptr;  // pinned
+    WfFrame* wf_host_frame = nullptr;    // pinned staging copy of the per-frame parameters
+    cudaGraph_t wf_graph[2] = {nullptr, nullptr};  // [0] plain, [1] with traversal counters
+    cudaGraphExec_t wf_exec[2] = {nullptr, nullptr};
+    uint32_t wf_graph_launches = 0;  // kernel nodes per graph launch
 
     ~RtScene() {
         cudaSetDevice(device);
@@ -55,8 +64,13 @@ struct RtScene {
         for (auto a : arrays) cudaFreeArray(a);
         for (auto p : allocs) cudaFree(p);
         if (accum) cudaFree(accum);
+        for (int g = 0; g < 2; g++) {
+            if (wf_exec[g]) cudaGraphExecDestroy(wf_exec[g]);
+            if (wf_graph[g]) cudaGraphDestroy(wf_graph[g]);
+        }
         for (auto p : wf_allocs) cudaFree(p);
         if (wf_host_counts) cudaFreeHost(wf_host_counts);
+        if (wf_host_frame) cudaFreeHost(wf_host_frame);
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
         if (stream) cudaStreamDestroy(stream);
@@ -147,11 +161,22 @@ bool tex_needs_uv(const RtFlatScene* d, uint32_t i, int depth = 0) {
     return false;
 }
 
+// Shading class of a material for the wavefront's material-sorted shade pass (rt_device.cuh CLS_*).
+uint32_t material_class(const RtFlatScene* d, const RtMaterial& m) {
+    if (m.kind >= RT_MAT_OREN_NAYAR) return (uint32_t)CLS_PBR;
+    if (m.kind == RT_MAT_METAL) return (uint32_t)CLS_METAL;
+    if (m.kind == RT_MAT_DIELECTRIC) return (uint32_t)CLS_DIELECTRIC;
+    if (m.kind == RT_MAT_DIFFUSE && d->textures[m.tex0].kind == RT_TEX_CONSTANT) return (uint32_t)CLS_DIFFUSE_CONST;
+    if (m.kind == RT_MAT_DIFFUSE && d->textures[m.tex0].kind == RT_TEX_PERLIN) return (uint32_t)CLS_DIFFUSE_PERLIN;
+    return (uint32_t)CLS_CLASSIC;
+}
+
 DevPrim make_dev_prim(const RtFlatScene* d, uint32_t flat, std::vector<DevMotion>& motion, const std::vector<uint32_t>& flat_to_dev) {
     const RtPrim& p = d->prims[flat];
     DevPrim q{};
     q.mat = p.mat;
-    q.kfx = (p.kind & 0xffu) | ((p.flags & 0xffu) << 8) | (p.xform << 16);
+    // kind | flags (4 bits) << 8 | shading class << 12 | transform chain << 16
+    q.kfx = (p.kind & 0xffu) | ((p.flags & 0xfu) << 8) | (material_class(d, d->materials[p.mat]) << 12) | (p.xform << 16);
     q.flat = flat;
     auto bits = [](uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; };
     auto ubits = [](float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; };
@@ -256,16 +281,8 @@ int rt_scene_create(const RtFlatScene* desc, int device, RtScene** out) {
         uint32_t flags = 0;
         if (t0 && tex_needs_uv(desc, m.tex0)) flags |= 1u;
         if (m.kind == RT_MAT_ROUGH_PLASTIC && tex_needs_uv(desc, m.tex1)) flags |= 1u;
-        // shading class for the wavefront's material-sorted shade pass (kernels.cuh WF_NCLASS)
-        const bool perlin = (t0 && tex_uses_kind(desc, m.tex0, RT_TEX_PERLIN)) ||
-                            (m.kind == RT_MAT_ROUGH_PLASTIC && tex_uses_kind(desc, m.tex1, RT_TEX_PERLIN));
-        const bool const_tex = t0 && desc->textures[m.tex0].kind == RT_TEX_CONSTANT;
-        uint32_t cls = 5u;
-        if (perlin) cls = 4u;
-        else if (m.kind >= RT_MAT_OREN_NAYAR) cls = 6u;
-        else if (m.kind == RT_MAT_DIFFUSE && const_tex) cls = 1u;
-        else if (m.kind == RT_MAT_METAL) cls = 2u;
-        else if (m.kind == RT_MAT_DIELECTRIC) cls = 3u;
+        const uint32_t cls = material_class(desc, m);
+        s->class_mask |= 1u << cls;
         flags |= cls << 8;
         mats[i] = DevMaterial{m.kind, m.tex0, m.tex1, flags, m.p[0], m.p[1], m.p[2], m.p[3]};
     }
@@ -439,76 +456,166 @@ int rt_camera_get_rays(const RtCamera* cam, const float* uv, size_t n, float* o_
     return RT_OK;
 }
 
+// The wavefront pool is split into `wf_chains` independent sub-pools.  Each chain runs its own
+// traverse -> shade -> traverse ... sequence; the chains share only the path counter, the frame
+// parameters, the accumulation buffer and the statistics, so the GPU overlaps one chain's kernel tails
+// and launch gaps with another chain's kernels.
+static uint32_t wf_chunk() { return (uint32_t)std::max(32, std::min(4096, env_int("RT_WF_CHUNK", 128))); }
+
 static int wf_ensure_pool(RtScene* s) {
-    if (s->wf.P) return RT_OK;
-    uint32_t P = (uint32_t)env_int("RT_WF_POOL", 1 << 20);
+    if (s->wf_chains) return RT_OK;
+    const int chains = std::max(1, std::min(WF_MAX_CHAINS, env_int("RT_WF_CHAINS", 4)));
+    uint32_t P = (uint32_t)env_int("RT_WF_POOL", 1 << 20) / (uint32_t)chains;
     P = std::max(256u * 32u, (P + 8191u) & ~8191u);
     auto alloc = [&](size_t bytes, void** out) -> cudaError_t {
         cudaError_t e = cudaMalloc(out, bytes);
         if (e == cudaSuccess) s->wf_allocs.push_back(*out);
         return e;
     };
-    CU_TRY(alloc((size_t)P * 16, (void**)&s->wf.ray_o));
-    CU_TRY(alloc((size_t)P * 16, (void**)&s->wf.ray_d));
-    CU_TRY(alloc((size_t)P * 16, (void**)&s->wf.beta));
-    CU_TRY(alloc((size_t)P * 8, (void**)&s->wf.rng));
-    CU_TRY(alloc((size_t)P * 8, (void**)&s->wf.hit));
-    CU_TRY(alloc((size_t)P * 4 * (WF_NCLASS - 1), (void**)&s->wf.queue));
-    CU_TRY(alloc(2 * WF_NCLASS * sizeof(uint32_t), (void**)&s->wf.n_class));
-    CU_TRY(alloc(sizeof(unsigned long long), (void**)&s->wf.path_counter));
-    CU_TRY(cudaMallocHost((void**)&s->wf_host_counts, 2 * WF_NCLASS * sizeof(uint32_t)));
-    s->wf.P = P;
+    unsigned long long* path_counter = nullptr;
+    WfFrame* frame = nullptr;
+    uint32_t* counters = nullptr;  // per chain: n_class[2][WF_NCLASS], trav_counter[2] (+ pad) = 32 words
+    CU_TRY(alloc(sizeof(unsigned long long), (void**)&path_counter));
+    CU_TRY(alloc(sizeof(WfFrame), (void**)&frame));
+    CU_TRY(alloc((size_t)chains * 32 * sizeof(uint32_t), (void**)&counters));
+    for (int c = 0; c < chains; c++) {
+        WfArgs& w = s->wf[c];
+        CU_TRY(alloc((size_t)P * 16, (void**)&w.ray_o));
+        CU_TRY(alloc((size_t)P * 16, (void**)&w.ray_d));
+        CU_TRY(alloc((size_t)P * 16, (void**)&w.beta));
+        CU_TRY(alloc((size_t)P * 8, (void**)&w.rng));
+        CU_TRY(alloc((size_t)P * 8, (void**)&w.hit));
+        CU_TRY(alloc((size_t)P * 4 * CLS_COUNT, (void**)&w.queue));
+        w.n_class = counters + c * 32;
+        w.trav_counter = counters + c * 32 + 2 * WF_NCLASS;
+        w.path_counter = path_counter;
+        w.frame = frame;
+        w.stats = s->stats;
+        w.P = P;
+    }
+    CU_TRY(cudaMallocHost((void**)&s->wf_host_counts, (size_t)chains * 32 * sizeof(uint32_t)));
+    CU_TRY(cudaMallocHost((void**)&s->wf_host_frame, sizeof(WfFrame)));
+    s->wf_chains = chains;
     return RT_OK;
 }
 
-// Wavefront frame: generate, then (traverse, shade) until the pool drains.  The loop needs the live count
-// on the host every few iterations, so this mode synchronises `st` internally.
+extern "C++" {
+template <uint32_t F>
+static void* wf_shade_fn(int cls) {
+    switch (cls) {
+        case CLS_MISS: return (void*)k_wf_shade<F, CLS_MISS>;
+        case CLS_DIFFUSE_CONST: return (void*)k_wf_shade<F, CLS_DIFFUSE_CONST>;
+        case CLS_METAL: return (void*)k_wf_shade<F, CLS_METAL>;
+        case CLS_DIELECTRIC: return (void*)k_wf_shade<F, CLS_DIELECTRIC>;
+        case CLS_DIFFUSE_PERLIN: return (void*)k_wf_shade<F, CLS_DIFFUSE_PERLIN>;
+        case CLS_CLASSIC: return (void*)k_wf_shade<F, CLS_CLASSIC>;
+        default: return (void*)k_wf_shade<F, CLS_PBR>;
+    }
+}
+}  // extern "C++"
+
+// Builds the graph of WF_GRAPH_ITERS iterations per chain: traverse -> {one shade kernel per class present} ->
+// traverse ...  Kernel arguments are per-scene constants (frame parameters are read from device memory), so the
+// graph is instantiated once per scene and variant.
+static int wf_ensure_graph(RtScene* s, bool count) {
+    const int g = count ? 1 : 0;
+    if (s->wf_exec[g]) return RT_OK;
+    const bool simple = s->features == 0;
+    void* trav_fn = simple ? (count ? (void*)k_wf_traverse<0u, true> : (void*)k_wf_traverse<0u, false>)
+                           : (count ? (void*)k_wf_traverse<F_ALL, true> : (void*)k_wf_traverse<F_ALL, false>);
+    int trav_bps = 0;
+    CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&trav_bps, trav_fn, WF_TRAV_THREADS, 0));
+    trav_bps = std::max(1, std::min(trav_bps, env_int("RT_WF_TRAV_BLOCKS", 64)));
+    const uint32_t P = s->wf[0].P;
+    // persistent traverse grid: what fits on the GPU, but never more warps than there are chunks of rays
+    const uint32_t trav_cap = std::max(1u, P / (wf_chunk() * WF_TRAV_WARPS));
+    const dim3 trav_grid(std::min<uint32_t>(trav_cap, (uint32_t)(s->sm_count * trav_bps)));
+    const uint32_t shade_cap = (P + WF_SHADE_THREADS - 1) / WF_SHADE_THREADS;
+    const dim3 shade_grid(std::min<uint32_t>(shade_cap, (uint32_t)(s->sm_count * env_int("RT_WF_SHADE_BLOCKS", 8))));
+    const uint32_t mask = s->class_mask | (1u << CLS_MISS);
+
+    cudaGraph_t graph = nullptr;
+    CU_TRY(cudaGraphCreate(&graph, 0));
+    s->wf_graph[g] = graph;
+    uint32_t n_nodes = 0;
+    for (int c = 0; c < s->wf_chains; c++) {
+        std::vector<cudaGraphNode_t> deps;
+        for (int it = 0; it < WF_GRAPH_ITERS; it++) {
+            int buf = it & 1;
+            void* args[3] = {(void*)&s->ds, (void*)&s->wf[c], (void*)&buf};
+            cudaKernelNodeParams kp{};
+            kp.func = trav_fn;
+            kp.gridDim = trav_grid;
+            kp.blockDim = dim3(WF_TRAV_THREADS);
+            kp.sharedMemBytes = 0;
+            kp.kernelParams = args;
+            cudaGraphNode_t trav = nullptr;
+            CU_TRY(cudaGraphAddKernelNode(&trav, graph, deps.data(), deps.size(), &kp));
+            n_nodes++;
+            deps.clear();
+            for (int cls = 0; cls < CLS_COUNT; cls++) {
+                if (!(mask & (1u << cls))) continue;
+                kp.func = simple ? wf_shade_fn<0u>(cls) : wf_shade_fn<F_ALL>(cls);
+                kp.gridDim = shade_grid;
+                kp.blockDim = dim3(WF_SHADE_THREADS);
+                cudaGraphNode_t sh = nullptr;
+                CU_TRY(cudaGraphAddKernelNode(&sh, graph, &trav, 1, &kp));
+                deps.push_back(sh);
+                n_nodes++;
+            }
+        }
+    }
+    CU_TRY(cudaGraphInstantiate(&s->wf_exec[g], graph, 0));
+    s->wf_graph_launches = n_nodes;
+    return RT_OK;
+}
+
+// Wavefront frame: generate, then graph launches of WF_GRAPH_ITERS x (traverse, shade classes) per chain until
+// the pools drain.  The loop needs the live count on the host, so this mode synchronises `st` internally.
 static int render_wavefront(RtScene* s, const RtRenderParams* rp, float* accum, cudaStream_t st, bool count, uint32_t* launches,
                             uint32_t* iterations) {
     int rc = wf_ensure_pool(s);
     if (rc != RT_OK) return rc;
-    WfArgs a = s->wf;
-    a.stats = s->stats;
-    a.accum = accum;
-    a.width = rp->width;
-    a.height = rp->height;
-    a.s_begin = rp->sample_begin;
-    a.n_samples = rp->sample_end - rp->sample_begin;
-    a.max_depth = rp->max_depth;
-    a.seed = rp->seed;
-    a.total_paths = (unsigned long long)rp->width * rp->height * a.n_samples;
-    CU_TRY(cudaMemsetAsync(a.n_class, 0, 2 * WF_NCLASS * sizeof(uint32_t), st));
-    CU_TRY(cudaMemsetAsync(a.path_counter, 0, sizeof(unsigned long long), st));
-    const uint32_t P = a.P;
-    k_wf_generate<<<P / 256, 256, 0, st>>>(s->ds, a);
-    *launches = 1;
-    const dim3 shade_grid((unsigned)(s->sm_count * env_int("RT_WF_SHADE_BLOCKS", 4)), WF_NCLASS - 1);
-    const bool simple = s->features == 0;
-    const unsigned long long min_iters = a.total_paths / P;  // every path needs at least one ray
-    int buf = 0;
+    rc = wf_ensure_graph(s, count);
+    if (rc != RT_OK) return rc;
+    const int chains = s->wf_chains;
+    WfFrame& f = *s->wf_host_frame;
+    f.accum = accum;
+    f.width = rp->width;
+    f.height = rp->height;
+    f.s_begin = rp->sample_begin;
+    f.n_samples = rp->sample_end - rp->sample_begin;
+    f.max_depth = rp->max_depth;
+    f.refill_threshold = (uint32_t)env_int("RT_WF_REFILL", 24);
+    f.chunk = wf_chunk();
+    f.seed = rp->seed;
+    f.total_paths = (unsigned long long)rp->width * rp->height * f.n_samples;
+    CU_TRY(cudaMemcpyAsync((void*)s->wf[0].frame, &f, sizeof(WfFrame), cudaMemcpyHostToDevice, st));
+    CU_TRY(cudaMemsetAsync(s->wf[0].n_class, 0, (size_t)chains * 32 * sizeof(uint32_t), st));
+    CU_TRY(cudaMemsetAsync(s->wf[0].path_counter, 0, sizeof(unsigned long long), st));
+    const uint32_t P = s->wf[0].P;
+    for (int c = 0; c < chains; c++) k_wf_generate<<<P / 256, 256, 0, st>>>(s->ds, s->wf[c]);
+    CU_TRY(cudaGetLastError());
+    *launches = (uint32_t)chains;
+    const unsigned long long min_iters = f.total_paths / ((unsigned long long)P * chains);  // every path needs at least one ray
+    const int last_buf = (WF_GRAPH_ITERS - 1) & 1;
     uint32_t it = 0;
-    for (;; it++) {
-        if (simple) {
-            if (count) k_wf_traverse<0u, true><<<P / WF_TRAV_THREADS, WF_TRAV_THREADS, 0, st>>>(s->ds, a, buf);
-            else k_wf_traverse<0u, false><<<P / WF_TRAV_THREADS, WF_TRAV_THREADS, 0, st>>>(s->ds, a, buf);
-            k_wf_shade<0u><<<shade_grid, WF_SHADE_THREADS, 0, st>>>(s->ds, a, buf);
-        } else {
-            if (count) k_wf_traverse<F_ALL, true><<<P / WF_TRAV_THREADS, WF_TRAV_THREADS, 0, st>>>(s->ds, a, buf);
-            else k_wf_traverse<F_ALL, false><<<P / WF_TRAV_THREADS, WF_TRAV_THREADS, 0, st>>>(s->ds, a, buf);
-            k_wf_shade<F_ALL><<<shade_grid, WF_SHADE_THREADS, 0, st>>>(s->ds, a, buf);
-        }
-        *launches += 2;
-        if (it >= min_iters && (it & 7u) == 7u) {
-            // n_class[buf][7] = number of live slots the last traverse saw (zeroed only by the NEXT shade)
-            CU_TRY(cudaMemcpyAsync(s->wf_host_counts, a.n_class, 2 * WF_NCLASS * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    for (;;) {
+        CU_TRY(cudaGraphLaunch(s->wf_exec[count ? 1 : 0], st));
+        *launches += s->wf_graph_launches;
+        it += WF_GRAPH_ITERS;
+        if (it >= min_iters) {
+            // n_class[buf][7] = number of rays the last traverse of each chain traced
+            CU_TRY(cudaMemcpyAsync(s->wf_host_counts, s->wf[0].n_class, (size_t)chains * 32 * sizeof(uint32_t),
+                                   cudaMemcpyDeviceToHost, st));
             CU_TRY(cudaStreamSynchronize(st));
-            if (s->wf_host_counts[buf * WF_NCLASS + 7] == 0) break;
+            uint32_t live = 0;
+            for (int c = 0; c < chains; c++) live += s->wf_host_counts[c * 32 + last_buf * WF_NCLASS + 7];
+            if (live == 0) break;
         }
-        buf ^= 1;
         if (it > 100000000u) return fail(RT_ERR_CUDA, "wavefront did not drain");
     }
-    CU_TRY(cudaGetLastError());
-    *iterations = it + 1;
+    *iterations = it;
     return RT_OK;
 }
 
