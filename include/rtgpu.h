@@ -244,7 +244,9 @@ int rt_camera_get_rays(const RtCamera* cam, const float* uv, size_t n, float* o_
 typedef enum RtRenderMode {
     RT_MODE_AUTO = 0,
     RT_MODE_MEGAKERNEL = 1, /* persistent per-thread path loop with in-warp path regeneration */
-    RT_MODE_WAVEFRONT = 2   /* raygen / traverse / shade+compact kernels over ray queues */
+    RT_MODE_WAVEFRONT = 2,  /* raygen / traverse / shade+compact kernels over ray queues in device memory */
+    RT_MODE_CTA_WAVEFRONT = 3 /* one persistent kernel; every thread block runs the wavefront loop on a
+                                 path pool and class queues held in its shared memory */
 } RtRenderMode;
 
 typedef struct RtRenderParams {

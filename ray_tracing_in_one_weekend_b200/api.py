@@ -26,7 +26,7 @@ XF_TRANSLATE, XF_ROTATE_Y = 0, 1
  MAT_ROUGH_PLASTIC, MAT_DISNEY_DIFFUSE, MAT_DISNEY_METAL, MAT_DISNEY_SHEEN, MAT_DISNEY_CLEARCOAT) = range(13)
 TEX_CONSTANT, TEX_CHECKER, TEX_PERLIN, TEX_IMAGE = range(4)
 SKY_GRADIENT, SKY_BLACK, SKY_ENVMAP, SKY_CONSTANT = range(4)
-MODE_AUTO, MODE_MEGAKERNEL, MODE_WAVEFRONT = range(3)
+MODE_AUTO, MODE_MEGAKERNEL, MODE_WAVEFRONT, MODE_CTA_WAVEFRONT = range(4)
 RENDER_COUNTERS = 1
 
 

@@ -21,7 +21,7 @@ CXX = os.environ.get("CXX", "g++")
 
 HOST_SRCS = ["scene_api.cpp", "demo_scene.cpp", "bvh_build.cpp"]
 CUDA_SRCS = ["rtgpu.cu"]
-HEADERS = ["scene_api.hpp", "bvh_build.hpp", "device_types.h", "rt_device.cuh", "kernels.cuh",
+HEADERS = ["scene_api.hpp", "bvh_build.hpp", "device_types.h", "rt_device.cuh", "kernels.cuh", "kernels_cta.cuh",
            os.path.join("..", "..", "include", "rtgpu.h")]
 
 HOST_FLAGS = ["-std=c++17", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-Wall"]

@@ -1,0 +1,329 @@
+// CTA-local wavefront renderer (sm_100a): the whole wavefront loop runs INSIDE one persistent kernel.
+//
+// Every thread block owns a pool of N paths in shared memory (64 B of path state + 16 B of queue space per
+// path, e.g. 768 paths = 60 KB, three blocks per SM out of Blackwell's 227 KB) and iterates, separated by
+// __syncthreads():
+//
+//   D  regenerate   one 64-bit atomicAdd per block and iteration reserves path indices for every path that
+//                   ended; threads generate the new camera rays (main.rs:88-93) into the dead slots
+//   A  traverse     warps pull path ids from a shared-memory counter, one ray per lane, while-while BVH
+//                   traversal (rt_device.cuh); a lane that finishes writes (t, prim) back and appends the path
+//                   to the shared-memory queue of its SHADING CLASS; idle lanes are refilled from the counter
+//                   as soon as `refill_idle` lanes of the warp are idle (shared-memory atomics make this cheap)
+//   C  shade        threads walk the class queues in class order (every class range padded to a warp
+//                   multiple, so a warp runs ONE material group): sky / emitted / scatter
+//                   (material.rs, pbr.rs, texture.rs), radiance to the frame with red.global.add.f32, the
+//                   scattered ray back into the slot, or the slot onto the dead list
+//
+// Nothing but the scene (L1-resident), the accumulation atomics and one counter atomic per block-iteration
+// touches global memory: no path-state traffic, no global queues, no kernel boundaries, no grid-wide tail
+// until the frame itself drains.  Blocks are independent; 2-3 resident blocks per SM fill each other's
+// barrier waits.  Replaces main.rs:38-60,84-97 with the same device functions and RNG streams as the other
+// two renderers (a path's stream depends only on (seed, pixel, global sample index)).
+#pragma once
+#include "kernels.cuh"
+
+namespace rtb {
+
+constexpr int CTA_THREADS = 256;
+constexpr int CTA_WARPS = CTA_THREADS / 32;
+constexpr int CTA_MIN_BLOCKS = 3;  // register cap 85: fits traversal and the common shading classes
+constexpr uint32_t CTA_NONE = 0xffffffffu;
+
+struct CtaArgs {
+    float* accum;
+    unsigned long long* path_counter;  // next unassigned path index of this launch (zeroed before launch)
+    unsigned long long* stats;         // [0] rays [1] shade calls [2..4] counters
+    unsigned long long total_paths;    // width * height * n_samples
+    uint32_t width, height, s_begin, max_depth;
+    uint32_t per_sample;   // width * height (< 2^31)
+    uint32_t n_paths;      // N: paths per block pool (multiple of 32, <= 4096)
+    uint32_t refill_idle;  // a warp retires/refills once this many of its lanes are idle
+    uint32_t pad0;
+    uint64_t seed;
+};
+
+// Bytes of dynamic shared memory for a pool of n paths.
+inline size_t cta_smem_bytes(uint32_t n) { return (size_t)n * (64 + 2 * (CLS_COUNT + 1)); }
+
+struct CtaPool {
+    float4* o;       // o.xyz, time
+    float4* d;       // d.xyz, bits(depth | alive << 31)
+    float4* b;       // throughput rgb, bits(pixel)
+    uint4* m;        // rng.lo, rng.hi, bits(t), prim
+    uint16_t* list;  // [CLS_COUNT][N] path ids per shading class
+    uint16_t* dead;  // [N] path ids to regenerate
+    uint32_t N;
+};
+
+// One queue entry of class CLS: the body of ray_color for a hit (main.rs:45-56) or a miss (main.rs:58).
+template <uint32_t F, int CLS>
+RT_DEV void cta_shade_item(const DeviceScene& sc, const CtaArgs& a, const CtaPool& P, uint32_t pid, uint32_t* s_ndead,
+                           uint32_t& n_shade) {
+    const float4 rd = P.d[pid], bt = P.b[pid];
+    Ray ray;
+    ray.d = mk3(rd.x, rd.y, rd.z);
+    ray.o = mk3(0.0f, 0.0f, 0.0f);
+    ray.tm = 0.0f;
+    V3f beta = mk3(bt.x, bt.y, bt.z);
+    const uint32_t pixel = __float_as_uint(bt.w);
+    uint32_t depth = __float_as_uint(rd.w) & 0xffu;
+    V3f add = mk3(0.0f, 0.0f, 0.0f);
+    bool alive = false;
+    PcgRng rng;
+    rng.state = 0;
+    if (CLS == CLS_MISS) {
+        // main.rs:58; a path dropped by the unit-direction check arrives here with beta == 0
+        if (beta.x != 0.0f || beta.y != 0.0f || beta.z != 0.0f) add = beta * sky_color(sc, ray.d);
+    } else {
+        const float4 ro = P.o[pid];
+        const uint4 mm = P.m[pid];
+        ray.o = mk3(ro.x, ro.y, ro.z);
+        ray.tm = ro.w;
+        rng.state = ((unsigned long long)mm.y << 32) | mm.x;
+        n_shade++;
+        DevPrim hp = load_prim(sc.prims, mm.w);
+        DevMaterial m = load_mat(sc, hp.mat);
+        const bool want_uv = (CLS == CLS_CLASSIC || CLS == CLS_PBR) && (m.reserved & 1u) != 0u;
+        HitRec rec = fill_hit<F>(sc, ray, mm.w, __uint_as_float(mm.z), want_uv);
+        V3f emitted, att;
+        Ray scattered;
+        bool ok = shade_cls<CLS>(sc, m, ray, rec, rng, emitted, att, scattered);
+        if (CLS == CLS_CLASSIC) add = beta * emitted;  // main.rs:47 (only Emission emits, material.rs:26-28)
+        if (ok) {                                      // main.rs:48-54
+            beta = beta * att;
+            ray = scattered;
+            depth++;
+            alive = depth <= a.max_depth;  // main.rs:40-42
+        }
+    }
+    if (add.x != 0.0f || add.y != 0.0f || add.z != 0.0f) {
+        float* px_out = a.accum + (size_t)pixel * 3u;
+        atomicAdd(px_out + 0, add.x);
+        atomicAdd(px_out + 1, add.y);
+        atomicAdd(px_out + 2, add.z);
+    }
+    if (alive) {
+        P.o[pid] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.tm);
+        P.d[pid] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(depth | WF_ALIVE));
+        P.b[pid] = make_float4(beta.x, beta.y, beta.z, bt.w);
+        uint2* st = reinterpret_cast<uint2*>(P.m + pid);
+        *st = make_uint2((uint32_t)rng.state, (uint32_t)(rng.state >> 32));
+    } else {
+        P.d[pid].w = __uint_as_float(0u);
+        const uint32_t pos = atomicAdd(s_ndead, 1u);
+        P.dead[pos] = (uint16_t)pid;
+    }
+}
+
+template <uint32_t F, bool COUNT>
+__global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(DeviceScene sc, CtaArgs a) {
+    extern __shared__ float4 cta_smem[];
+    __shared__ uint32_t s_cnt[8];  // per-class queue lengths of this iteration
+    __shared__ uint32_t s_next;    // next pool slot the traverse phase hands out
+    __shared__ uint32_t s_ndead;   // entries of the dead list
+    __shared__ uint32_t s_live;    // live paths of the pool
+    __shared__ uint32_t s_nregen, s_r0, s_s0;
+
+    const uint32_t tid = threadIdx.x, lane = tid & 31u;
+    const uint32_t N = a.n_paths;
+    CtaPool P;
+    P.o = cta_smem;
+    P.d = P.o + N;
+    P.b = P.d + N;
+    P.m = reinterpret_cast<uint4*>(P.b + N);
+    P.list = reinterpret_cast<uint16_t*>(P.m + N);
+    P.dead = P.list + (size_t)CLS_COUNT * N;
+    P.N = N;
+
+    for (uint32_t i = tid; i < N; i += CTA_THREADS) {
+        P.d[i] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(0u));
+        P.dead[i] = (uint16_t)i;
+    }
+    if (tid == 0) {
+        s_ndead = N;
+        s_live = N;  // every slot "dies" once before the first iteration
+    }
+    uint32_t n_rays = 0, n_shade = 0;
+    TravCounters tc;
+    uint2 stack[STACK_SIZE];
+    __syncthreads();
+
+    for (;;) {
+        // ================================================================== D: regenerate ended paths
+        if (tid == 0) {
+            const uint32_t n_dead = s_ndead;
+            uint32_t n_regen = 0;
+            if (n_dead) {
+                const unsigned long long base = atomicAdd(a.path_counter, (unsigned long long)n_dead);
+                if (base < a.total_paths) {
+                    const unsigned long long left = a.total_paths - base;
+                    n_regen = left < (unsigned long long)n_dead ? (uint32_t)left : n_dead;
+                    s_s0 = (uint32_t)(base / a.per_sample);
+                    s_r0 = (uint32_t)(base % a.per_sample);
+                }
+            }
+            s_nregen = n_regen;
+            s_live = s_live - n_dead + n_regen;
+            s_ndead = 0u;
+            s_next = 0u;
+#pragma unroll
+            for (int c = 0; c < 8; c++) s_cnt[c] = 0u;
+        }
+        __syncthreads();
+        if (s_live == 0u) break;
+        {
+            const uint32_t n_regen = s_nregen;
+            for (uint32_t i = tid; i < n_regen; i += CTA_THREADS) {
+                const uint32_t pid = P.dead[i];
+                // path index k = base + i  ->  (sample, pixel) = divmod(k, width * height), main.rs:84-93
+                uint32_t r = s_r0 + i, s = s_s0;
+                while (r >= a.per_sample) {
+                    r -= a.per_sample;
+                    s++;
+                }
+                const uint32_t py = r / a.width, px = r - py * a.width;
+                PcgRng rng;
+                rng.seed(a.seed, r, a.s_begin + s);
+                const float u = ((float)px + rng.next()) / (float)a.width;
+                const float v = ((float)py + rng.next()) / (float)a.height;
+                const Ray ray = camera_get_ray(sc.cam, u, v, rng);
+                P.o[pid] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.tm);
+                P.d[pid] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(WF_ALIVE));
+                P.b[pid] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(r));
+                uint2* st = reinterpret_cast<uint2*>(P.m + pid);
+                *st = make_uint2((uint32_t)rng.state, (uint32_t)(rng.state >> 32));
+            }
+        }
+        __syncthreads();
+
+        // ================================================================== A: traverse (one ray per lane)
+        {
+            uint32_t pid = CTA_NONE;
+            bool more = true;  // the pool may still hold slots nobody has looked at (warp-uniform)
+            Ray ray;
+            ray.o = ray.d = mk3(0.0f, 0.0f, 0.0f);
+            ray.tm = 0.0f;
+            RaySlab rs;
+            rs.init(ray);
+            TravState ts;
+            ts.init(0.0f);
+            ts.cur = TRAV_NONE;
+            XformCache xc;
+            xc.chain = 0;
+            xc.ro = ray;
+            PcgRng rng;
+            rng.state = 0;
+            for (;;) {
+                // ---- retire finished lanes: hit record back to the slot, slot id to its class queue
+                if (pid != CTA_NONE && ts.cur == TRAV_NONE) {
+                    uint2* hit = reinterpret_cast<uint2*>(P.m + pid) + 1;
+                    *hit = make_uint2(__float_as_uint(ts.best_t), ts.best_prim);
+                    if (F & F_MEDIA) {
+                        uint2* st = reinterpret_cast<uint2*>(P.m + pid);
+                        *st = make_uint2((uint32_t)rng.state, (uint32_t)(rng.state >> 32));
+                    }
+                    const uint32_t cls = ts.best_prim == 0xffffffffu ? (uint32_t)CLS_MISS : ((ts.best_kfx >> 12) & 0xfu);
+                    const uint32_t pos = atomicAdd(&s_cnt[cls], 1u);
+                    P.list[cls * N + pos] = (uint16_t)pid;
+                    pid = CTA_NONE;
+                }
+                // ---- refill idle lanes from the block's slot counter
+                while (more) {
+                    const uint32_t wm = __ballot_sync(0xffffffffu, pid == CTA_NONE);
+                    if (wm == 0u) break;
+                    uint32_t base = 0;
+                    if (lane == 0) base = atomicAdd(&s_next, (uint32_t)__popc(wm));
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    if (base + (uint32_t)__popc(wm) >= N) more = false;
+                    const uint32_t idx = base + (uint32_t)__popc(wm & ((1u << lane) - 1u));
+                    if (pid == CTA_NONE && idx < N) {
+                        const float4 rd = P.d[idx];
+                        if (__float_as_uint(rd.w) & WF_ALIVE) {
+                            const float4 ro = P.o[idx];
+                            pid = idx;
+                            n_rays++;
+                            ray.o = mk3(ro.x, ro.y, ro.z);
+                            ray.d = mk3(rd.x, rd.y, rd.z);
+                            ray.tm = ro.w;
+                            ts.init(3.402823466e+38f);
+                            if (F & F_XFORM) {
+                                xc.chain = 0;
+                                xc.ro = ray;
+                            }
+                            if (F & F_MEDIA) {
+                                const uint2 st = *reinterpret_cast<const uint2*>(P.m + idx);
+                                rng.state = ((unsigned long long)st.y << 32) | st.x;
+                            }
+                            if (vec3a_near_one(ray.d)) {
+                                rs.init(ray);
+                            } else {
+                                // main.rs:39: a non-unit direction loses the path; it retires as a miss with zero throughput
+                                P.b[idx] = make_float4(0.0f, 0.0f, 0.0f, P.b[idx].w);
+                                ts.cur = TRAV_NONE;
+                            }
+                        }
+                    }
+                }
+                if (!__any_sync(0xffffffffu, pid != CTA_NONE)) break;
+                // ---- traverse until enough lanes are idle again (and there is something to refill them with)
+                for (;;) {
+                    while (!(ts.cur & LEAF_FLAG) && ts.cur != TRAV_NONE) node_visit<COUNT>(sc, rs, 1e-3f, ts, stack, &tc);
+                    if (ts.cur != TRAV_NONE) {
+                        leaf_visit<F, COUNT>(sc, ray, 1e-3f, ts, xc, rng, false, &tc);
+                        ts.pop(stack);
+                    }
+                    const uint32_t busy = __ballot_sync(0xffffffffu, ts.cur != TRAV_NONE);
+                    if (busy == 0u) break;
+                    if (more && 32u - (uint32_t)__popc(busy) >= a.refill_idle) break;
+                }
+            }
+        }
+        __syncthreads();
+
+        // ================================================================== C: shade, class by class
+        {
+            uint32_t start[CLS_COUNT + 1];  // class ranges in a common index space, each padded to a warp multiple
+            start[0] = 0u;
+#pragma unroll
+            for (int c = 0; c < CLS_COUNT; c++) start[c + 1] = start[c] + ((s_cnt[c] + 31u) & ~31u);
+            for (uint32_t g = tid; g < start[CLS_COUNT]; g += CTA_THREADS) {
+                int cls = 0;
+#pragma unroll
+                for (int c = 1; c < CLS_COUNT; c++) cls += g >= start[c] ? 1 : 0;
+                uint32_t first = 0;
+#pragma unroll
+                for (int c = 1; c < CLS_COUNT; c++) first = cls == c ? start[c] : first;
+                const uint32_t idx = g - first;
+                if (idx >= s_cnt[cls]) continue;
+                const uint32_t pid = P.list[(uint32_t)cls * N + idx];
+                switch (cls) {
+                    case CLS_MISS: cta_shade_item<F, CLS_MISS>(sc, a, P, pid, &s_ndead, n_shade); break;
+                    case CLS_DIFFUSE_CONST: cta_shade_item<F, CLS_DIFFUSE_CONST>(sc, a, P, pid, &s_ndead, n_shade); break;
+                    case CLS_METAL: cta_shade_item<F, CLS_METAL>(sc, a, P, pid, &s_ndead, n_shade); break;
+                    case CLS_DIELECTRIC: cta_shade_item<F, CLS_DIELECTRIC>(sc, a, P, pid, &s_ndead, n_shade); break;
+                    case CLS_DIFFUSE_PERLIN: cta_shade_item<F, CLS_DIFFUSE_PERLIN>(sc, a, P, pid, &s_ndead, n_shade); break;
+                    case CLS_CLASSIC: cta_shade_item<F, CLS_CLASSIC>(sc, a, P, pid, &s_ndead, n_shade); break;
+                    default: cta_shade_item<F, CLS_PBR>(sc, a, P, pid, &s_ndead, n_shade); break;
+                }
+            }
+        }
+        __syncthreads();
+    }
+
+    const unsigned long long rays = warp_sum_u64(n_rays), shades = warp_sum_u64(n_shade);
+    if (lane == 0) {
+        atomicAdd(a.stats + 0, rays);
+        atomicAdd(a.stats + 1, shades);
+    }
+    if (COUNT) {
+        unsigned long long nv = warp_sum_u64(tc.node_visits), bt = warp_sum_u64(tc.box_tests), pt = warp_sum_u64(tc.prim_tests);
+        if (lane == 0) {
+            atomicAdd(a.stats + 2, nv);
+            atomicAdd(a.stats + 3, bt);
+            atomicAdd(a.stats + 4, pt);
+        }
+    }
+}
+
+}  // namespace rtb

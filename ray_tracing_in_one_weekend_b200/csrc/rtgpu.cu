@@ -11,6 +11,7 @@
 
 #include "bvh_build.hpp"
 #include "kernels.cuh"
+#include "kernels_cta.cuh"
 #include "scene_api.hpp"
 
 using namespace rtb;
@@ -41,6 +42,7 @@ struct RtScene {
     RtCamera camera{};
     // render scratch
     unsigned int* work_counter = nullptr;
+    unsigned long long* cta_path_counter = nullptr;
     unsigned long long* stats = nullptr;
     float* accum = nullptr;
     size_t accum_floats = 0;
@@ -379,6 +381,9 @@ int rt_scene_create(const RtFlatScene* desc, int device, RtScene** out) {
     CU_TRY(cudaMalloc(&p, 8 * sizeof(unsigned long long)));
     s->allocs.push_back(p);
     s->stats = (unsigned long long*)p;
+    CU_TRY(cudaMalloc(&p, sizeof(unsigned long long)));
+    s->allocs.push_back(p);
+    s->cta_path_counter = (unsigned long long*)p;
     // the traversal stack lives in local memory: make sure L1 is preferred over shared memory
     if (s->features == 0) {
         CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->mega_blocks_per_sm, k_render_mega<0u, false>, MEGA_THREADS, 0));
@@ -622,9 +627,65 @@ static int render_wavefront(RtScene* s, const RtRenderParams* rp, float* accum, 
 int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* cuda_stream, RtStats* stats) {
     if (!s || !rp || !accum) return fail(RT_ERR_ARG, "NULL argument");
     if (rp->width == 0 || rp->height == 0 || rp->sample_end < rp->sample_begin) return fail(RT_ERR_ARG, "bad render params");
-    if (rp->mode > RT_MODE_WAVEFRONT) return fail(RT_ERR_ARG, "bad render mode");
+    if (rp->mode > RT_MODE_CTA_WAVEFRONT) return fail(RT_ERR_ARG, "bad render mode");
     uint32_t mode = rp->mode;
     if (mode == RT_MODE_AUTO) mode = (uint32_t)env_int("RT_DEFAULT_MODE", RT_MODE_MEGAKERNEL);
+    if (mode == RT_MODE_CTA_WAVEFRONT && rp->sample_end > rp->sample_begin) {
+        auto w0 = std::chrono::steady_clock::now();
+        CU_TRY(cudaSetDevice(s->device));
+        cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : s->stream;
+        const bool count = (rp->flags & RT_RENDER_COUNTERS) != 0;
+        if ((uint64_t)rp->width * rp->height >= (1ull << 31)) return fail(RT_ERR_ARG, "image too large");
+        CU_TRY(cudaMemsetAsync(s->stats, 0, 8 * sizeof(unsigned long long), st));
+        CU_TRY(cudaMemsetAsync(s->cta_path_counter, 0, sizeof(unsigned long long), st));
+        CtaArgs a{};
+        a.accum = accum;
+        a.path_counter = s->cta_path_counter;
+        a.stats = s->stats;
+        a.width = rp->width;
+        a.height = rp->height;
+        a.s_begin = rp->sample_begin;
+        a.max_depth = rp->max_depth;
+        a.per_sample = rp->width * rp->height;
+        a.total_paths = (unsigned long long)a.per_sample * (rp->sample_end - rp->sample_begin);
+        a.n_paths = (uint32_t)std::max(32, std::min(4096, env_int("RT_CTA_PATHS", 768))) & ~31u;
+        a.refill_idle = (uint32_t)std::max(1, std::min(32, env_int("RT_CTA_REFILL", 8)));
+        a.seed = rp->seed;
+        const size_t smem = cta_smem_bytes(a.n_paths);
+        void* fn = s->features == 0 ? (count ? (void*)k_render_cta<0u, true> : (void*)k_render_cta<0u, false>)
+                                    : (count ? (void*)k_render_cta<F_ALL, true> : (void*)k_render_cta<F_ALL, false>);
+        CU_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int bps = 0;
+        CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, fn, CTA_THREADS, smem));
+        if (bps < 1) return fail(RT_ERR_CUDA, "CTA wavefront kernel does not fit on an SM");
+        bps = std::min(bps, env_int("RT_CTA_BLOCKS", 64));
+        // never more blocks than there are pools of work
+        const unsigned long long want = (a.total_paths + a.n_paths - 1) / a.n_paths;
+        const unsigned grid = (unsigned)std::max<unsigned long long>(1, std::min<unsigned long long>(want, (unsigned long long)s->sm_count * bps));
+        CU_TRY(cudaEventRecord(s->ev0, st));
+        void* args[2] = {(void*)&s->ds, (void*)&a};
+        CU_TRY(cudaLaunchKernel(fn, dim3(grid), dim3(CTA_THREADS), args, smem, st));
+        CU_TRY(cudaEventRecord(s->ev1, st));
+        if (stats) {
+            std::memset(stats, 0, sizeof(*stats));
+            unsigned long long h[8] = {0};
+            CU_TRY(cudaMemcpyAsync(h, s->stats, sizeof(h), cudaMemcpyDeviceToHost, st));
+            CU_TRY(cudaStreamSynchronize(st));
+            float ms = 0.0f;
+            CU_TRY(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+            stats->ms_kernel = ms;
+            stats->paths = a.total_paths;
+            stats->rays = h[0];
+            stats->shade_calls = h[1];
+            stats->node_visits = h[2];
+            stats->box_tests = h[3];
+            stats->prim_tests = h[4];
+            stats->launches = 1;
+            stats->mode_used = RT_MODE_CTA_WAVEFRONT;
+            stats->ms_total = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - w0).count();
+        }
+        return RT_OK;
+    }
     if (mode == RT_MODE_WAVEFRONT && rp->sample_end > rp->sample_begin) {
         auto w0 = std::chrono::steady_clock::now();
         CU_TRY(cudaSetDevice(s->device));
