@@ -44,7 +44,7 @@ struct CtaArgs {
 };
 
 // Bytes of dynamic shared memory for a pool of n paths.
-inline size_t cta_smem_bytes(uint32_t n) { return (size_t)n * (64 + 2 * (CLS_COUNT + 1)); }
+inline size_t cta_smem_bytes(uint32_t n) { return (size_t)n * (64 + 2 * (CLS_COUNT + 2)); }
 
 struct CtaPool {
     float4* o;       // o.xyz, time
@@ -53,13 +53,14 @@ struct CtaPool {
     uint4* m;        // rng.lo, rng.hi, bits(t), prim
     uint16_t* list;  // [CLS_COUNT][N] path ids per shading class
     uint16_t* dead;  // [N] path ids to regenerate
+    uint16_t* todo;  // [N] path ids to traverse next: scattered paths (in shading order), then the regenerated ones
     uint32_t N;
 };
 
 // One queue entry of class CLS: the body of ray_color for a hit (main.rs:45-56) or a miss (main.rs:58).
 template <uint32_t F, int CLS>
 RT_DEV void cta_shade_item(const DeviceScene& sc, const CtaArgs& a, const CtaPool& P, uint32_t pid, uint32_t* s_ndead,
-                           uint32_t& n_shade) {
+                           uint32_t* s_ntodo, uint32_t& n_shade) {
     const float4 rd = P.d[pid], bt = P.b[pid];
     Ray ray;
     ray.d = mk3(rd.x, rd.y, rd.z);
@@ -109,6 +110,7 @@ RT_DEV void cta_shade_item(const DeviceScene& sc, const CtaArgs& a, const CtaPoo
         P.b[pid] = make_float4(beta.x, beta.y, beta.z, bt.w);
         uint2* st = reinterpret_cast<uint2*>(P.m + pid);
         *st = make_uint2((uint32_t)rng.state, (uint32_t)(rng.state >> 32));
+        P.todo[atomicAdd(s_ntodo, 1u)] = (uint16_t)pid;
     } else {
         P.d[pid].w = __uint_as_float(0u);
         const uint32_t pos = atomicAdd(s_ndead, 1u);
@@ -116,14 +118,66 @@ RT_DEV void cta_shade_item(const DeviceScene& sc, const CtaArgs& a, const CtaPoo
     }
 }
 
+// Traversal registers of one lane.
+struct CtaLane {
+    uint32_t pid;
+    Ray ray;
+    RaySlab rs;
+    TravState ts;
+    XformCache xc;
+    PcgRng rng;
+};
+
+// Load the ray of pool slot `idx` into the lane and set its traversal up (main.rs:39-44).
+template <uint32_t F>
+RT_DEV void cta_fetch(const CtaPool& P, uint32_t idx, CtaLane& L) {
+    const float4 rd = P.d[idx], ro = P.o[idx];
+    L.pid = idx;
+    L.ray.o = mk3(ro.x, ro.y, ro.z);
+    L.ray.d = mk3(rd.x, rd.y, rd.z);
+    L.ray.tm = ro.w;
+    L.ts.init(3.402823466e+38f);
+    if (F & F_XFORM) {
+        L.xc.chain = 0;
+        L.xc.ro = L.ray;
+    }
+    if (F & F_MEDIA) {
+        const uint2 st = *reinterpret_cast<const uint2*>(P.m + idx);
+        L.rng.state = ((unsigned long long)st.y << 32) | st.x;
+    }
+    if (vec3a_near_one(L.ray.d)) {
+        L.rs.init(L.ray);
+    } else {
+        // main.rs:39: a non-unit direction loses the path; it retires as a miss with zero throughput
+        P.b[idx] = make_float4(0.0f, 0.0f, 0.0f, P.b[idx].w);
+        L.ts.cur = TRAV_NONE;
+    }
+}
+
+// Traversal of the lane's ray is complete: hit record back to the slot, slot id to its class queue.
+template <uint32_t F>
+RT_DEV void cta_retire(const CtaPool& P, CtaLane& L, uint32_t* s_cnt) {
+    uint2* hit = reinterpret_cast<uint2*>(P.m + L.pid) + 1;
+    *hit = make_uint2(__float_as_uint(L.ts.best_t), L.ts.best_prim);
+    if (F & F_MEDIA) {
+        uint2* st = reinterpret_cast<uint2*>(P.m + L.pid);
+        *st = make_uint2((uint32_t)L.rng.state, (uint32_t)(L.rng.state >> 32));
+    }
+    const uint32_t cls = L.ts.best_prim == 0xffffffffu ? (uint32_t)CLS_MISS : ((L.ts.best_kfx >> 12) & 0xfu);
+    const uint32_t pos = atomicAdd(&s_cnt[cls], 1u);
+    P.list[cls * P.N + pos] = (uint16_t)L.pid;
+    L.pid = CTA_NONE;
+}
+
 template <uint32_t F, bool COUNT>
 __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(DeviceScene sc, CtaArgs a) {
     extern __shared__ float4 cta_smem[];
     __shared__ uint32_t s_cnt[8];  // per-class queue lengths of this iteration
-    __shared__ uint32_t s_next;    // next pool slot the traverse phase hands out
+    __shared__ uint32_t s_next;    // next entry of the scattered part of the todo list the traverse phase hands out
+    __shared__ uint32_t s_nextp;   // next entry of the regenerated (camera ray) part
     __shared__ uint32_t s_ndead;   // entries of the dead list
-    __shared__ uint32_t s_live;    // live paths of the pool
-    __shared__ uint32_t s_nregen, s_r0, s_s0;
+    __shared__ uint32_t s_ntodo;   // scattered paths appended to the todo list by the shade phase
+    __shared__ uint32_t s_nsurv, s_nregen, s_r0, s_s0;
 
     const uint32_t tid = threadIdx.x, lane = tid & 31u;
     const uint32_t N = a.n_paths;
@@ -134,6 +188,7 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
     P.m = reinterpret_cast<uint4*>(P.b + N);
     P.list = reinterpret_cast<uint16_t*>(P.m + N);
     P.dead = P.list + (size_t)CLS_COUNT * N;
+    P.todo = P.dead + N;
     P.N = N;
 
     for (uint32_t i = tid; i < N; i += CTA_THREADS) {
@@ -141,8 +196,8 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
         P.dead[i] = (uint16_t)i;
     }
     if (tid == 0) {
-        s_ndead = N;
-        s_live = N;  // every slot "dies" once before the first iteration
+        s_ndead = N;  // every slot "dies" once before the first iteration
+        s_ntodo = 0u;
     }
     uint32_t n_rays = 0, n_shade = 0;
     TravCounters tc;
@@ -164,116 +219,97 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
                 }
             }
             s_nregen = n_regen;
-            s_live = s_live - n_dead + n_regen;
+            s_nsurv = s_ntodo;
+            s_ntodo = 0u;
             s_ndead = 0u;
             s_next = 0u;
+            s_nextp = 0u;
 #pragma unroll
             for (int c = 0; c < 8; c++) s_cnt[c] = 0u;
         }
         __syncthreads();
-        if (s_live == 0u) break;
-        {
-            const uint32_t n_regen = s_nregen;
-            for (uint32_t i = tid; i < n_regen; i += CTA_THREADS) {
-                const uint32_t pid = P.dead[i];
-                // path index k = base + i  ->  (sample, pixel) = divmod(k, width * height), main.rs:84-93
-                uint32_t r = s_r0 + i, s = s_s0;
-                while (r >= a.per_sample) {
-                    r -= a.per_sample;
-                    s++;
-                }
-                const uint32_t py = r / a.width, px = r - py * a.width;
-                PcgRng rng;
-                rng.seed(a.seed, r, a.s_begin + s);
-                const float u = ((float)px + rng.next()) / (float)a.width;
-                const float v = ((float)py + rng.next()) / (float)a.height;
-                const Ray ray = camera_get_ray(sc.cam, u, v, rng);
-                P.o[pid] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.tm);
-                P.d[pid] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(WF_ALIVE));
-                P.b[pid] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(r));
-                uint2* st = reinterpret_cast<uint2*>(P.m + pid);
-                *st = make_uint2((uint32_t)rng.state, (uint32_t)(rng.state >> 32));
+        const uint32_t n_regen = s_nregen, n_surv = s_nsurv;
+        if (n_regen + n_surv == 0u) break;
+        for (uint32_t i = tid; i < n_regen; i += CTA_THREADS) {
+            const uint32_t pid = P.dead[i];
+            // path index k = base + i  ->  (sample, pixel) = divmod(k, width * height), main.rs:84-93
+            uint32_t r = s_r0 + i, s = s_s0;
+            while (r >= a.per_sample) {
+                r -= a.per_sample;
+                s++;
             }
+            const uint32_t py = r / a.width, px = r - py * a.width;
+            PcgRng rng;
+            rng.seed(a.seed, r, a.s_begin + s);
+            const float u = ((float)px + rng.next()) / (float)a.width;
+            const float v = ((float)py + rng.next()) / (float)a.height;
+            const Ray ray = camera_get_ray(sc.cam, u, v, rng);
+            P.o[pid] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.tm);
+            P.d[pid] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(WF_ALIVE));
+            P.b[pid] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(r));
+            uint2* st = reinterpret_cast<uint2*>(P.m + pid);
+            *st = make_uint2((uint32_t)rng.state, (uint32_t)(rng.state >> 32));
+            P.todo[n_surv + i] = (uint16_t)pid;  // consecutive pixels of a row sit next to each other
         }
         __syncthreads();
 
         // ================================================================== A: traverse (one ray per lane)
         {
-            uint32_t pid = CTA_NONE;
-            bool more = true;  // the pool may still hold slots nobody has looked at (warp-uniform)
-            Ray ray;
-            ray.o = ray.d = mk3(0.0f, 0.0f, 0.0f);
-            ray.tm = 0.0f;
-            RaySlab rs;
-            rs.init(ray);
-            TravState ts;
-            ts.init(0.0f);
-            ts.cur = TRAV_NONE;
-            XformCache xc;
-            xc.chain = 0;
-            xc.ro = ray;
-            PcgRng rng;
-            rng.state = 0;
+            CtaLane L;
+            L.pid = CTA_NONE;
+            L.ray.o = L.ray.d = mk3(0.0f, 0.0f, 0.0f);
+            L.ray.tm = 0.0f;
+            L.rs.init(L.ray);
+            L.ts.init(0.0f);
+            L.ts.cur = TRAV_NONE;
+            L.xc.chain = 0;
+            L.xc.ro = L.ray;
+            L.rng.state = 0;
+            // ---- A1: camera rays, 32 neighbouring pixels per warp: coherent, so the warp runs them to completion
             for (;;) {
-                // ---- retire finished lanes: hit record back to the slot, slot id to its class queue
-                if (pid != CTA_NONE && ts.cur == TRAV_NONE) {
-                    uint2* hit = reinterpret_cast<uint2*>(P.m + pid) + 1;
-                    *hit = make_uint2(__float_as_uint(ts.best_t), ts.best_prim);
-                    if (F & F_MEDIA) {
-                        uint2* st = reinterpret_cast<uint2*>(P.m + pid);
-                        *st = make_uint2((uint32_t)rng.state, (uint32_t)(rng.state >> 32));
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(&s_nextp, 32u);
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (base >= n_regen) break;
+                if (base + lane < n_regen) {
+                    cta_fetch<F>(P, P.todo[n_surv + base + lane], L);
+                    n_rays++;
+                    while (L.ts.cur != TRAV_NONE) {
+                        while (!(L.ts.cur & LEAF_FLAG) && L.ts.cur != TRAV_NONE) node_visit<COUNT>(sc, L.rs, 1e-3f, L.ts, stack, &tc);
+                        if (L.ts.cur == TRAV_NONE) break;
+                        leaf_visit<F, COUNT>(sc, L.ray, 1e-3f, L.ts, L.xc, L.rng, false, &tc);
+                        L.ts.pop(stack);
                     }
-                    const uint32_t cls = ts.best_prim == 0xffffffffu ? (uint32_t)CLS_MISS : ((ts.best_kfx >> 12) & 0xfu);
-                    const uint32_t pos = atomicAdd(&s_cnt[cls], 1u);
-                    P.list[cls * N + pos] = (uint16_t)pid;
-                    pid = CTA_NONE;
+                    cta_retire<F>(P, L, s_cnt);
                 }
-                // ---- refill idle lanes from the block's slot counter
+                __syncwarp();
+            }
+            // ---- A2: scattered rays (incoherent): idle lanes are refilled from the block's counter
+            bool more = n_surv != 0u;  // the todo list may still hold entries nobody has looked at (warp-uniform)
+            for (;;) {
+                if (L.pid != CTA_NONE && L.ts.cur == TRAV_NONE) cta_retire<F>(P, L, s_cnt);
                 while (more) {
-                    const uint32_t wm = __ballot_sync(0xffffffffu, pid == CTA_NONE);
+                    const uint32_t wm = __ballot_sync(0xffffffffu, L.pid == CTA_NONE);
                     if (wm == 0u) break;
                     uint32_t base = 0;
                     if (lane == 0) base = atomicAdd(&s_next, (uint32_t)__popc(wm));
                     base = __shfl_sync(0xffffffffu, base, 0);
-                    if (base + (uint32_t)__popc(wm) >= N) more = false;
+                    if (base + (uint32_t)__popc(wm) >= n_surv) more = false;
                     const uint32_t idx = base + (uint32_t)__popc(wm & ((1u << lane) - 1u));
-                    if (pid == CTA_NONE && idx < N) {
-                        const float4 rd = P.d[idx];
-                        if (__float_as_uint(rd.w) & WF_ALIVE) {
-                            const float4 ro = P.o[idx];
-                            pid = idx;
-                            n_rays++;
-                            ray.o = mk3(ro.x, ro.y, ro.z);
-                            ray.d = mk3(rd.x, rd.y, rd.z);
-                            ray.tm = ro.w;
-                            ts.init(3.402823466e+38f);
-                            if (F & F_XFORM) {
-                                xc.chain = 0;
-                                xc.ro = ray;
-                            }
-                            if (F & F_MEDIA) {
-                                const uint2 st = *reinterpret_cast<const uint2*>(P.m + idx);
-                                rng.state = ((unsigned long long)st.y << 32) | st.x;
-                            }
-                            if (vec3a_near_one(ray.d)) {
-                                rs.init(ray);
-                            } else {
-                                // main.rs:39: a non-unit direction loses the path; it retires as a miss with zero throughput
-                                P.b[idx] = make_float4(0.0f, 0.0f, 0.0f, P.b[idx].w);
-                                ts.cur = TRAV_NONE;
-                            }
-                        }
+                    if (L.pid == CTA_NONE && idx < n_surv) {
+                        cta_fetch<F>(P, P.todo[idx], L);
+                        n_rays++;
                     }
                 }
-                if (!__any_sync(0xffffffffu, pid != CTA_NONE)) break;
+                if (!__any_sync(0xffffffffu, L.pid != CTA_NONE)) break;
                 // ---- traverse until enough lanes are idle again (and there is something to refill them with)
                 for (;;) {
-                    while (!(ts.cur & LEAF_FLAG) && ts.cur != TRAV_NONE) node_visit<COUNT>(sc, rs, 1e-3f, ts, stack, &tc);
-                    if (ts.cur != TRAV_NONE) {
-                        leaf_visit<F, COUNT>(sc, ray, 1e-3f, ts, xc, rng, false, &tc);
-                        ts.pop(stack);
+                    while (!(L.ts.cur & LEAF_FLAG) && L.ts.cur != TRAV_NONE) node_visit<COUNT>(sc, L.rs, 1e-3f, L.ts, stack, &tc);
+                    if (L.ts.cur != TRAV_NONE) {
+                        leaf_visit<F, COUNT>(sc, L.ray, 1e-3f, L.ts, L.xc, L.rng, false, &tc);
+                        L.ts.pop(stack);
                     }
-                    const uint32_t busy = __ballot_sync(0xffffffffu, ts.cur != TRAV_NONE);
+                    const uint32_t busy = __ballot_sync(0xffffffffu, L.ts.cur != TRAV_NONE);
                     if (busy == 0u) break;
                     if (more && 32u - (uint32_t)__popc(busy) >= a.refill_idle) break;
                 }
@@ -298,13 +334,13 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
                 if (idx >= s_cnt[cls]) continue;
                 const uint32_t pid = P.list[(uint32_t)cls * N + idx];
                 switch (cls) {
-                    case CLS_MISS: cta_shade_item<F, CLS_MISS>(sc, a, P, pid, &s_ndead, n_shade); break;
-                    case CLS_DIFFUSE_CONST: cta_shade_item<F, CLS_DIFFUSE_CONST>(sc, a, P, pid, &s_ndead, n_shade); break;
-                    case CLS_METAL: cta_shade_item<F, CLS_METAL>(sc, a, P, pid, &s_ndead, n_shade); break;
-                    case CLS_DIELECTRIC: cta_shade_item<F, CLS_DIELECTRIC>(sc, a, P, pid, &s_ndead, n_shade); break;
-                    case CLS_DIFFUSE_PERLIN: cta_shade_item<F, CLS_DIFFUSE_PERLIN>(sc, a, P, pid, &s_ndead, n_shade); break;
-                    case CLS_CLASSIC: cta_shade_item<F, CLS_CLASSIC>(sc, a, P, pid, &s_ndead, n_shade); break;
-                    default: cta_shade_item<F, CLS_PBR>(sc, a, P, pid, &s_ndead, n_shade); break;
+                    case CLS_MISS: cta_shade_item<F, CLS_MISS>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
+                    case CLS_DIFFUSE_CONST: cta_shade_item<F, CLS_DIFFUSE_CONST>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
+                    case CLS_METAL: cta_shade_item<F, CLS_METAL>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
+                    case CLS_DIELECTRIC: cta_shade_item<F, CLS_DIELECTRIC>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
+                    case CLS_DIFFUSE_PERLIN: cta_shade_item<F, CLS_DIFFUSE_PERLIN>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
+                    case CLS_CLASSIC: cta_shade_item<F, CLS_CLASSIC>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
+                    default: cta_shade_item<F, CLS_PBR>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
                 }
             }
         }
