@@ -33,6 +33,9 @@ WIDTH, HEIGHT = 1920, 1080
 MAX_DEPTH = 50
 
 
+KERNEL_NAMES = {1: "k_render_mega", 2: "k_wf_traverse + k_wf_shade (CUDA graph)", 3: "k_render_cta"}
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -43,7 +46,7 @@ def parse_args():
     ap.add_argument("--scene", default=SCENE)
     ap.add_argument("--width", type=int, default=WIDTH)
     ap.add_argument("--height", type=int, default=HEIGHT)
-    ap.add_argument("--mode", type=int, default=0, help="RtRenderMode: 0 auto, 1 megakernel, 2 wavefront")
+    ap.add_argument("--mode", type=int, default=0, help="RtRenderMode: 0 auto (= 3), 1 megakernel, 2 wavefront, 3 CTA-local wavefront")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -288,9 +291,19 @@ def run_ours(args, rank, world, local_rank):
             "node_visits": cst.node_visits / max(1, cst.rays), "box_tests": cst.box_tests / max(1, cst.rays),
             "prim_tests": cst.prim_tests / max(1, cst.rays), "p_hit": cst.shade_calls / max(1, cst.rays),
         }
-        # algorithmic FP32 ops per ray, constants of SURVEY.md 8(d): C_box 27, C_sph 24 (+10 per evaluated
-        # root ~ per hit), C_fill 46, C_shade ~80 (Diffuse-dominated; Perlin ground not counted -> lower bound)
-        f_ray = 27.0 * per_ray["box_tests"] + 24.0 * per_ray["prim_tests"] + (10.0 + 46.0 + 80.0) * per_ray["p_hit"]
+        # algorithmic FP32 ops per ray, constants of SURVEY.md 8(d): C_box 27 per slab test, C_sph 24 per sphere
+        # test (+10 when a root is evaluated ~ per hit), C_fill 46 per hit, C_shade per shading class (counted by
+        # the RT_RENDER_COUNTERS build: rays per class): sky 11, Diffuse 80, Metal 60, Dielectric 70,
+        # Diffuse+Perlin 80 + 7*(8*(3+11)+30) = 1074, other material.rs combinations >= 5 (Emission; lower bound),
+        # pbr.rs 170.
+        C_CLS = [11.0, 80.0, 60.0, 70.0, 1074.0, 5.0, 170.0]
+        cls = [int(x) for x in cst.class_counts][:7]
+        if sum(cls) == cst.rays and cst.rays:
+            shade_ops = sum((c * (C_CLS[i] + (56.0 if i else 0.0))) for i, c in enumerate(cls)) / cst.rays
+            per_ray["class_share"] = [c / cst.rays for c in cls]
+        else:  # renderer without class counters: Diffuse-dominated estimate, Perlin not counted (lower bound)
+            shade_ops = (10.0 + 46.0 + 80.0) * per_ray["p_hit"]
+        f_ray = 27.0 * per_ray["box_tests"] + 24.0 * per_ray["prim_tests"] + shade_ops
         rays_per_launch = rays_per_step / world
         achieved = rays_per_launch * f_ray / (ms_kernel * 1e-3) / 1e12
         peak = peak_ffma / 1e12
@@ -316,10 +329,10 @@ def run_ours(args, rank, world, local_rank):
             "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(W * H * 12), "steps": e2e_steps,
                     "what": "rt_scene_create (H2D of all scene tables + host BVH build) + render + reduce + divide + D2H of the float frame, per step"},
-            "gpu_launches": args.steps * 1,
+            "gpu_launches": int(args.steps * st.launches),
             "roofline": {"bound": "fp32-issue", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
                          "traffic": None,
-                         "note": "k_render_mega; achieved = algorithmic FP32 ops per ray (SURVEY 8d constants, counted on this BVH) "
+                         "note": KERNEL_NAMES.get(int(st.mode_used), "?") + "; achieved = algorithmic FP32 ops per ray (SURVEY 8d constants, counted on this BVH) "
                                  "x rays per launch / CUDA-event kernel time; peak = MEASURED lane-FFMA issue rate of this GPU "
                                  "(rt_measure_fp32_peak, 1 op per lane-slot), of measured",
                          "ops_per_ray": f_ray, "per_ray": per_ray, "ms_kernel": ms_kernel,

@@ -274,6 +274,9 @@ typedef struct RtStats {
     double ms_total;       /* host wall clock of the call, including copies */
     uint32_t launches;     /* kernels launched by this call */
     uint32_t mode_used;
+    uint64_t class_counts[8]; /* only with RT_RENDER_COUNTERS in RT_MODE_CTA_WAVEFRONT: rays per shading class
+                                 (0 miss/sky, 1 Diffuse(ConstantTex), 2 Metal, 3 Dielectric, 4 Diffuse(PerlinTex),
+                                 5 other material.rs combinations, 6 pbr.rs materials) */
 } RtStats;
 
 /* Renders global samples [sample_begin, sample_end) and ADDS the radiance SUMS (not means) to the

@@ -13,7 +13,7 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 REPO = os.path.dirname(HERE)
-LIB_PATH = os.path.join(HERE, "librtgpu.so")
+LIB_PATH = os.environ.get("RTGPU_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "librtgpu.so")  # RTGPU_LIB: development override
 ASSET_DIR = os.path.join(REPO, "assets")
 
 RT_ABI_VERSION = 1
@@ -113,10 +113,11 @@ class RtRenderParams(C.Structure):
 class RtStats(C.Structure):
     _fields_ = [("paths", C.c_uint64), ("rays", C.c_uint64), ("node_visits", C.c_uint64), ("box_tests", C.c_uint64),
                 ("prim_tests", C.c_uint64), ("shade_calls", C.c_uint64), ("ms_kernel", C.c_double),
-                ("ms_total", C.c_double), ("launches", C.c_uint32), ("mode_used", C.c_uint32)]
+                ("ms_total", C.c_double), ("launches", C.c_uint32), ("mode_used", C.c_uint32),
+                ("class_counts", C.c_uint64 * 8)]
 
     def as_dict(self) -> dict:
-        return {n: getattr(self, n) for n, _ in self._fields_}
+        return {n: (list(getattr(self, n)) if n == "class_counts" else getattr(self, n)) for n, _ in self._fields_}
 
 
 # every symbol include/rtgpu.h declares

@@ -25,15 +25,21 @@
 
 namespace rtb {
 
-constexpr int CTA_THREADS = 256;
+#ifndef RT_CTA_THREADS
+#define RT_CTA_THREADS 384
+#endif
+#ifndef RT_CTA_MIN_BLOCKS
+#define RT_CTA_MIN_BLOCKS 2  // register cap 85 (80 used): fits traversal and the common shading classes
+#endif
+constexpr int CTA_THREADS = RT_CTA_THREADS;
 constexpr int CTA_WARPS = CTA_THREADS / 32;
-constexpr int CTA_MIN_BLOCKS = 3;  // register cap 85: fits traversal and the common shading classes
+constexpr int CTA_MIN_BLOCKS = RT_CTA_MIN_BLOCKS;
 constexpr uint32_t CTA_NONE = 0xffffffffu;
 
 struct CtaArgs {
     float* accum;
     unsigned long long* path_counter;  // next unassigned path index of this launch (zeroed before launch)
-    unsigned long long* stats;         // [0] rays [1] shade calls [2..4] counters
+    unsigned long long* stats;         // [0] rays [1] shade calls [2..4] counters [8..14] rays per shading class
     unsigned long long total_paths;    // width * height * n_samples
     uint32_t width, height, s_begin, max_depth;
     uint32_t per_sample;   // width * height (< 2^31)
@@ -200,8 +206,13 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
         s_ntodo = 0u;
     }
     uint32_t n_rays = 0, n_shade = 0;
+    unsigned long long cls_total[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // thread 0, COUNT builds only
     TravCounters tc;
     uint2 stack[STACK_SIZE];
+    if (tid == 0) {
+#pragma unroll
+        for (int c = 0; c < 8; c++) s_cnt[c] = 0u;
+    }
     __syncthreads();
 
     for (;;) {
@@ -225,7 +236,10 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
             s_next = 0u;
             s_nextp = 0u;
 #pragma unroll
-            for (int c = 0; c < 8; c++) s_cnt[c] = 0u;
+            for (int c = 0; c < 8; c++) {
+                if (COUNT) cls_total[c] += s_cnt[c];
+                s_cnt[c] = 0u;
+            }
         }
         __syncthreads();
         const uint32_t n_regen = s_nregen, n_surv = s_nsurv;
@@ -358,6 +372,10 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
             atomicAdd(a.stats + 2, nv);
             atomicAdd(a.stats + 3, bt);
             atomicAdd(a.stats + 4, pt);
+        }
+        if (tid == 0) {
+#pragma unroll
+            for (int c = 0; c < CLS_COUNT; c++) atomicAdd(a.stats + 8 + c, cls_total[c]);
         }
     }
 }

@@ -378,7 +378,7 @@ int rt_scene_create(const RtFlatScene* desc, int device, RtScene** out) {
     CU_TRY(cudaMalloc(&p, sizeof(unsigned int)));
     s->allocs.push_back(p);
     s->work_counter = (unsigned int*)p;
-    CU_TRY(cudaMalloc(&p, 8 * sizeof(unsigned long long)));
+    CU_TRY(cudaMalloc(&p, 16 * sizeof(unsigned long long)));
     s->allocs.push_back(p);
     s->stats = (unsigned long long*)p;
     CU_TRY(cudaMalloc(&p, sizeof(unsigned long long)));
@@ -629,14 +629,14 @@ int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* c
     if (rp->width == 0 || rp->height == 0 || rp->sample_end < rp->sample_begin) return fail(RT_ERR_ARG, "bad render params");
     if (rp->mode > RT_MODE_CTA_WAVEFRONT) return fail(RT_ERR_ARG, "bad render mode");
     uint32_t mode = rp->mode;
-    if (mode == RT_MODE_AUTO) mode = (uint32_t)env_int("RT_DEFAULT_MODE", RT_MODE_MEGAKERNEL);
+    if (mode == RT_MODE_AUTO) mode = (uint32_t)env_int("RT_DEFAULT_MODE", RT_MODE_CTA_WAVEFRONT);
     if (mode == RT_MODE_CTA_WAVEFRONT && rp->sample_end > rp->sample_begin) {
         auto w0 = std::chrono::steady_clock::now();
         CU_TRY(cudaSetDevice(s->device));
         cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : s->stream;
         const bool count = (rp->flags & RT_RENDER_COUNTERS) != 0;
         if ((uint64_t)rp->width * rp->height >= (1ull << 31)) return fail(RT_ERR_ARG, "image too large");
-        CU_TRY(cudaMemsetAsync(s->stats, 0, 8 * sizeof(unsigned long long), st));
+        CU_TRY(cudaMemsetAsync(s->stats, 0, 16 * sizeof(unsigned long long), st));
         CU_TRY(cudaMemsetAsync(s->cta_path_counter, 0, sizeof(unsigned long long), st));
         CtaArgs a{};
         a.accum = accum;
@@ -648,7 +648,7 @@ int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* c
         a.max_depth = rp->max_depth;
         a.per_sample = rp->width * rp->height;
         a.total_paths = (unsigned long long)a.per_sample * (rp->sample_end - rp->sample_begin);
-        a.n_paths = (uint32_t)std::max(32, std::min(4096, env_int("RT_CTA_PATHS", 768))) & ~31u;
+        a.n_paths = (uint32_t)std::max(32, std::min(4096, env_int("RT_CTA_PATHS", 3 * CTA_THREADS))) & ~31u;
         a.refill_idle = (uint32_t)std::max(1, std::min(32, env_int("RT_CTA_REFILL", 8)));
         a.seed = rp->seed;
         const size_t smem = cta_smem_bytes(a.n_paths);
@@ -668,7 +668,7 @@ int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* c
         CU_TRY(cudaEventRecord(s->ev1, st));
         if (stats) {
             std::memset(stats, 0, sizeof(*stats));
-            unsigned long long h[8] = {0};
+            unsigned long long h[16] = {0};
             CU_TRY(cudaMemcpyAsync(h, s->stats, sizeof(h), cudaMemcpyDeviceToHost, st));
             CU_TRY(cudaStreamSynchronize(st));
             float ms = 0.0f;
@@ -682,6 +682,7 @@ int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* c
             stats->prim_tests = h[4];
             stats->launches = 1;
             stats->mode_used = RT_MODE_CTA_WAVEFRONT;
+            for (int c = 0; c < 8; c++) stats->class_counts[c] = h[8 + c];
             stats->ms_total = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - w0).count();
         }
         return RT_OK;

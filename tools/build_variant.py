@@ -1,0 +1,31 @@
+#!/usr/bin/env python3
+"""Development tool: build a variant of librtgpu.so with extra nvcc flags into variants/<name>/librtgpu.so.
+
+    python tools/build_variant.py t224b4 -DRT_CTA_THREADS=224 -DRT_CTA_MIN_BLOCKS=4
+    RTGPU_LIB=variants/t224b4/librtgpu.so python tools/mode_sweep.py ...
+"""
+import os, subprocess, sys
+sys.path.insert(0, os.getcwd())
+from ray_tracing_in_one_weekend_b200 import build as b
+
+name, extra = sys.argv[1], sys.argv[2:]
+b.build_all()
+out = os.path.join("variants", name)
+os.makedirs(out, exist_ok=True)
+obj = os.path.join(os.path.abspath(out), "rtgpu.o")
+r = subprocess.run([b.NVCC] + b.NVCC_FLAGS + extra + ["-c", "rtgpu.cu", "-o", obj], cwd=b.CSRC, capture_output=True, text=True)
+if r.returncode:
+    sys.stderr.write(r.stderr)
+    raise SystemExit(1)
+for l in (r.stdout + r.stderr).splitlines():
+    if "k_render_cta" in l and "Compiling" in l:
+        want = True
+        print(l.split("'")[1][:40], end=" ")
+    elif "registers" in l and locals().get("want"):
+        print(l.strip()); want = False
+    elif "spill" in l and locals().get("want"):
+        print(l.strip(), end=" | ")
+objs = [os.path.join(b.CSRC, s.replace(".cpp", ".o")) for s in b.HOST_SRCS] + [obj]
+subprocess.check_call([b.NVCC, "-shared", "-o", os.path.join(out, "librtgpu.so")] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"])
+os.remove(obj)
+print(os.path.join(out, "librtgpu.so"))
