@@ -181,6 +181,7 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
     __shared__ uint32_t s_cnt[8];  // per-class queue lengths of this iteration
     __shared__ uint32_t s_next;    // next entry of the scattered part of the todo list the traverse phase hands out
     __shared__ uint32_t s_nextp;   // next entry of the regenerated (camera ray) part
+    __shared__ uint32_t s_chunk;   // next 32-entry chunk of the shade phase
     __shared__ uint32_t s_ndead;   // entries of the dead list
     __shared__ uint32_t s_ntodo;   // scattered paths appended to the todo list by the shade phase
     __shared__ uint32_t s_nsurv, s_nregen, s_r0, s_s0;
@@ -235,6 +236,7 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
             s_ndead = 0u;
             s_next = 0u;
             s_nextp = 0u;
+            s_chunk = 0u;
 #pragma unroll
             for (int c = 0; c < 8; c++) {
                 if (COUNT) cls_total[c] += s_cnt[c];
@@ -333,29 +335,43 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
 
         // ================================================================== C: shade, class by class
         {
-            uint32_t start[CLS_COUNT + 1];  // class ranges in a common index space, each padded to a warp multiple
+            // Class ranges in a common index space, each padded to a warp multiple, the most expensive class
+            // first; warps pull 32-entry chunks from a counter (longest-processing-time-first keeps the tail short).
+            constexpr int ORDER[CLS_COUNT] = {CLS_DIFFUSE_PERLIN, CLS_PBR, CLS_CLASSIC, CLS_DIELECTRIC,
+                                              CLS_DIFFUSE_CONST, CLS_METAL, CLS_MISS};
+            uint32_t start[CLS_COUNT + 1];
             start[0] = 0u;
 #pragma unroll
-            for (int c = 0; c < CLS_COUNT; c++) start[c + 1] = start[c] + ((s_cnt[c] + 31u) & ~31u);
-            for (uint32_t g = tid; g < start[CLS_COUNT]; g += CTA_THREADS) {
-                int cls = 0;
+            for (int c = 0; c < CLS_COUNT; c++) start[c + 1] = start[c] + ((s_cnt[ORDER[c]] + 31u) & ~31u);
+            for (;;) {
+                uint32_t g = 0;
+                if (lane == 0) g = atomicAdd(&s_chunk, 32u);
+                g = __shfl_sync(0xffffffffu, g, 0);
+                if (g >= start[CLS_COUNT]) break;
+                int k = 0;
 #pragma unroll
-                for (int c = 1; c < CLS_COUNT; c++) cls += g >= start[c] ? 1 : 0;
+                for (int c = 1; c < CLS_COUNT; c++) k += g >= start[c] ? 1 : 0;
                 uint32_t first = 0;
+                int cls = ORDER[0];
 #pragma unroll
-                for (int c = 1; c < CLS_COUNT; c++) first = cls == c ? start[c] : first;
-                const uint32_t idx = g - first;
-                if (idx >= s_cnt[cls]) continue;
-                const uint32_t pid = P.list[(uint32_t)cls * N + idx];
-                switch (cls) {
-                    case CLS_MISS: cta_shade_item<F, CLS_MISS>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
-                    case CLS_DIFFUSE_CONST: cta_shade_item<F, CLS_DIFFUSE_CONST>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
-                    case CLS_METAL: cta_shade_item<F, CLS_METAL>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
-                    case CLS_DIELECTRIC: cta_shade_item<F, CLS_DIELECTRIC>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
-                    case CLS_DIFFUSE_PERLIN: cta_shade_item<F, CLS_DIFFUSE_PERLIN>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
-                    case CLS_CLASSIC: cta_shade_item<F, CLS_CLASSIC>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
-                    default: cta_shade_item<F, CLS_PBR>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
+                for (int c = 1; c < CLS_COUNT; c++) {
+                    first = k == c ? start[c] : first;
+                    cls = k == c ? ORDER[c] : cls;
                 }
+                const uint32_t idx = g - first + lane;
+                if (idx < s_cnt[cls]) {
+                    const uint32_t pid = P.list[(uint32_t)cls * N + idx];
+                    switch (cls) {
+                        case CLS_MISS: cta_shade_item<F, CLS_MISS>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
+                        case CLS_DIFFUSE_CONST: cta_shade_item<F, CLS_DIFFUSE_CONST>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
+                        case CLS_METAL: cta_shade_item<F, CLS_METAL>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
+                        case CLS_DIELECTRIC: cta_shade_item<F, CLS_DIELECTRIC>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
+                        case CLS_DIFFUSE_PERLIN: cta_shade_item<F, CLS_DIFFUSE_PERLIN>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
+                        case CLS_CLASSIC: cta_shade_item<F, CLS_CLASSIC>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
+                        default: cta_shade_item<F, CLS_PBR>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
+                    }
+                }
+                __syncwarp();
             }
         }
         __syncthreads();

@@ -1,4 +1,2 @@
-timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/c6_pytest.log 2>&1; tail -3 gpurun_out/c6_pytest.log
-python bench.py > gpurun_out/c6_bench.json 2> gpurun_out/c6_bench.err; cat gpurun_out/c6_bench.json; tail -3 gpurun_out/c6_bench.err
-python tools/mode_sweep.py sphere_scene 1920 1080 8 3 > gpurun_out/c6_plain.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:k_render_cta -s 1 -c 1 -o gpurun_out/prof_cta2 python tools/mode_sweep.py sphere_scene 1920 1080 8 3 > gpurun_out/c6_ncu.log 2>&1
-tail -2 gpurun_out/c6_ncu.log
+timeout 600 python -m pytest tests/test_gpu_render.py -m gpu -x -q -k "cta_wavefront or agree" > gpurun_out/c7_pytest.log 2>&1; tail -3 gpurun_out/c7_pytest.log
+for s in sphere_scene cornell_box final_scene pbr_ibl cover_100k_motion; do timeout 300 python tools/mode_sweep.py $s 1920 1080 32 3 2>&1 | tee -a gpurun_out/c7_scenes.log; done
