@@ -281,25 +281,6 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
             L.xc.chain = 0;
             L.xc.ro = L.ray;
             L.rng.state = 0;
-            // ---- A1: camera rays, 32 neighbouring pixels per warp: coherent, so the warp runs them to completion
-            for (;;) {
-                uint32_t base = 0;
-                if (lane == 0) base = atomicAdd(&s_nextp, 32u);
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (base >= n_regen) break;
-                if (base + lane < n_regen) {
-                    cta_fetch<F>(P, P.todo[n_surv + base + lane], L);
-                    n_rays++;
-                    while (L.ts.cur != TRAV_NONE) {
-                        while (!(L.ts.cur & LEAF_FLAG) && L.ts.cur != TRAV_NONE) node_visit<COUNT>(sc, L.rs, 1e-3f, L.ts, stack, &tc);
-                        if (L.ts.cur == TRAV_NONE) break;
-                        leaf_visit<F, COUNT>(sc, L.ray, 1e-3f, L.ts, L.xc, L.rng, false, &tc);
-                        L.ts.pop(stack);
-                    }
-                    cta_retire<F>(P, L, s_cnt);
-                }
-                __syncwarp();
-            }
             // ---- A2: scattered rays (incoherent): idle lanes are refilled from the block's counter
             bool more = n_surv != 0u;  // the todo list may still hold entries nobody has looked at (warp-uniform)
             for (;;) {
@@ -329,6 +310,25 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
                     if (busy == 0u) break;
                     if (more && 32u - (uint32_t)__popc(busy) >= a.refill_idle) break;
                 }
+            }
+            // ---- A1: camera rays, 32 neighbouring pixels per warp: coherent, so the warp runs them to completion
+            for (;;) {
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(&s_nextp, 32u);
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (base >= n_regen) break;
+                if (base + lane < n_regen) {
+                    cta_fetch<F>(P, P.todo[n_surv + base + lane], L);
+                    n_rays++;
+                    while (L.ts.cur != TRAV_NONE) {
+                        while (!(L.ts.cur & LEAF_FLAG) && L.ts.cur != TRAV_NONE) node_visit<COUNT>(sc, L.rs, 1e-3f, L.ts, stack, &tc);
+                        if (L.ts.cur == TRAV_NONE) break;
+                        leaf_visit<F, COUNT>(sc, L.ray, 1e-3f, L.ts, L.xc, L.rng, false, &tc);
+                        L.ts.pop(stack);
+                    }
+                    cta_retire<F>(P, L, s_cnt);
+                }
+                __syncwarp();
             }
         }
         __syncthreads();
