@@ -21,6 +21,7 @@ CXX = os.environ.get("CXX", "g++")
 
 HOST_SRCS = ["scene_api.cpp", "demo_scene.cpp", "bvh_build.cpp"]
 CUDA_SRCS = ["rtgpu.cu"]
+CTA_FEATURE_SETS = [0, 4, 8, 9, 11, 15]  # cta_inst.cu is compiled once per set (kernels_cta.cuh)
 HEADERS = ["scene_api.hpp", "bvh_build.hpp", "device_types.h", "rt_device.cuh", "kernels.cuh", "kernels_cta.cuh",
            os.path.join("..", "..", "include", "rtgpu.h")]
 
@@ -56,11 +57,21 @@ def build_all(force: bool = False, verbose: bool = False) -> str:
         if force or _stale(obj, [os.path.join(CSRC, src)] + hdrs):
             log.append(_run([CXX] + HOST_FLAGS + ["-c", src, "-o", obj]))
         objs.append(obj)
+    jobs = []
     for src in CUDA_SRCS:
         obj = os.path.join(CSRC, src.replace(".cu", ".o"))
         if force or _stale(obj, [os.path.join(CSRC, src)] + hdrs):
-            log.append(_run([NVCC] + NVCC_FLAGS + ["-c", src, "-o", obj]))
+            jobs.append([NVCC] + NVCC_FLAGS + ["-c", src, "-o", obj])
         objs.append(obj)
+    for f in CTA_FEATURE_SETS:
+        obj = os.path.join(CSRC, f"cta_f{f}.o")
+        if force or _stale(obj, [os.path.join(CSRC, "cta_inst.cu")] + hdrs):
+            jobs.append([NVCC] + NVCC_FLAGS + [f"-DRT_CTA_F={f}", "-c", "cta_inst.cu", "-o", obj])
+        objs.append(obj)
+    if jobs:  # the CUDA units are independent: compile them side by side
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(max_workers=min(len(jobs), os.cpu_count() or 4)) as ex:
+            log.extend(ex.map(_run, jobs))
     if force or _stale(LIB, objs):
         log.append(_run([NVCC, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"]))
     out = "".join(log)

@@ -61,11 +61,6 @@ struct RenderArgs {
 
 constexpr int MEGA_THREADS = 128;
 
-RT_DEV unsigned long long warp_sum_u64(unsigned long long v) {
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
-}
-
 template <uint32_t F, bool COUNT>
 __global__ void __launch_bounds__(MEGA_THREADS) k_render_mega(DeviceScene sc, RenderArgs a) {
     const uint32_t lane = threadIdx.x & 31u;
@@ -219,7 +214,6 @@ struct WfArgs {
     uint32_t P;
 };
 
-constexpr uint32_t WF_ALIVE = 0x80000000u;
 constexpr uint32_t WF_NO_SLOT = 0xffffffffu;
 
 // New camera path for a slot (main.rs:88-93).  Path index k -> (sample, pixel): k = s * (W*H) + pixel, pixels

@@ -21,7 +21,7 @@
 // barrier waits.  Replaces main.rs:38-60,84-97 with the same device functions and RNG streams as the other
 // two renderers (a path's stream depends only on (seed, pixel, global sample index)).
 #pragma once
-#include "kernels.cuh"
+#include "rt_device.cuh"
 
 namespace rtb {
 
@@ -394,6 +394,29 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
             for (int c = 0; c < CLS_COUNT; c++) atomicAdd(a.stats + 8 + c, cls_total[c]);
         }
     }
+}
+
+// Host-side entry points, one translation unit per instantiated feature set (cta_inst.cu, -DRT_CTA_F=<F>).
+// Feature sets built: 0 (spheres only), F_MOTION, F_RECT, F_RECT|F_XFORM, F_RECT|F_XFORM|F_MEDIA, F_ALL.
+void* cta_kernel_f0(bool count);
+void* cta_kernel_f4(bool count);
+void* cta_kernel_f8(bool count);
+void* cta_kernel_f9(bool count);
+void* cta_kernel_f11(bool count);
+void* cta_kernel_f15(bool count);
+
+// The kernel of the smallest built feature set that covers `features`.
+inline void* cta_kernel_for(uint32_t features, bool count, uint32_t* built) {
+    struct E { uint32_t f; void* (*fn)(bool); };
+    const E table[] = {{0u, cta_kernel_f0}, {4u, cta_kernel_f4}, {8u, cta_kernel_f8}, {9u, cta_kernel_f9},
+                       {11u, cta_kernel_f11}, {15u, cta_kernel_f15}};
+    for (const E& e : table)
+        if ((features & ~e.f) == 0u) {
+            if (built) *built = e.f;
+            return e.fn(count);
+        }
+    if (built) *built = 15u;
+    return cta_kernel_f15(count);
 }
 
 }  // namespace rtb

@@ -652,8 +652,7 @@ int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* c
         a.refill_idle = (uint32_t)std::max(1, std::min(32, env_int("RT_CTA_REFILL", 8)));
         a.seed = rp->seed;
         const size_t smem = cta_smem_bytes(a.n_paths);
-        void* fn = s->features == 0 ? (count ? (void*)k_render_cta<0u, true> : (void*)k_render_cta<0u, false>)
-                                    : (count ? (void*)k_render_cta<F_ALL, true> : (void*)k_render_cta<F_ALL, false>);
+        void* fn = cta_kernel_for(s->features, count, nullptr);
         CU_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         int bps = 0;
         CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, fn, CTA_THREADS, smem));
