@@ -209,6 +209,15 @@ DevPrim make_dev_prim(const RtFlatScene* d, uint32_t flat, std::vector<DevMotion
             q.g0 = p.g[0];
             q.g1 = bits(flat_to_dev[p.aux0]);
             q.g2 = bits(p.aux1);
+            {  // g3 = 1: the boundary is <= 6 rects under one transform chain (medium_test's single-pass path)
+                bool box = p.aux1 <= 6;
+                for (uint32_t k = 0; k < p.aux1 && box; k++) {
+                    const RtPrim& b = d->prims[p.aux0 + k];
+                    box = (b.kind == RT_PRIM_XYRECT || b.kind == RT_PRIM_XZRECT || b.kind == RT_PRIM_YZRECT) &&
+                          b.xform == d->prims[p.aux0].xform;
+                }
+                q.g3 = bits(box ? 1u : 0u);
+            }
             break;
     }
     return q;
