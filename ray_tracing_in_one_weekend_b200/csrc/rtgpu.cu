@@ -296,6 +296,14 @@ int rt_scene_create(const RtFlatScene* desc, int device, RtScene** out) {
         s->class_mask |= 1u << cls;
         flags |= cls << 8;
         mats[i] = DevMaterial{m.kind, m.tex0, m.tex1, flags, m.p[0], m.p[1], m.p[2], m.p[3]};
+        if (cls == (uint32_t)CLS_DIFFUSE_CONST) {
+            // Diffuse has no parameters of its own (material.rs:31-33): keep the ConstantTex colour in the
+            // material record so the class-specialised shader needs one table lookup, not two
+            const RtTexture& t = desc->textures[m.tex0];
+            mats[i].p0 = t.p[0];
+            mats[i].p1 = t.p[1];
+            mats[i].p2 = t.p[2];
+        }
     }
     std::vector<DevTexture> texs(desc->n_textures);
     for (uint32_t i = 0; i < desc->n_textures; i++) {
