@@ -246,7 +246,7 @@ int rt_scene_create(const RtFlatScene* desc, int device, RtScene** out) {
 
     BvhBuildResult bvh;
     try {
-        build_bvh4(*desc, (uint32_t)env_int("RT_LEAF_MAX", 4), bvh);
+        build_bvh4(*desc, (uint32_t)env_int("RT_LEAF_MAX", 1), bvh);
     } catch (const std::exception& e) {
         return fail(RT_ERR_ARG, e.what());
     }
