@@ -262,13 +262,10 @@ def run_ours(args, rank, world, local_rank):
     flat = hs.flat.contents
     h2d = (flat.n_prims * 32 + info.n_nodes * info.node_bytes + flat.n_materials * 32 + flat.n_textures * 32 +
            flat.n_perlin * (4096 + 768) + sum(flat.images[i].width * flat.images[i].height * 4 for i in range(flat.n_images)))
-    barrier()
-    e2e_steps = max(1, min(args.steps, 3))
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
+    def e2e_step(spp_params):
         sc2 = rt.Scene(hs.flat, local_rank)  # flattened scene (host) -> device: H2D of every table + BVH build
         accum.zero_()
-        sc2.render_device(params, accum.data_ptr(), stream.cuda_stream, want_stats=False)
+        sc2.render_device(spp_params, accum.data_ptr(), stream.cuda_stream, want_stats=False)
         if world > 1:
             dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
         if rank == 0:
@@ -276,6 +273,16 @@ def run_ours(args, rank, world, local_rank):
             host_out.copy_(accum, non_blocking=True)  # D2H read of the frame
         torch.cuda.synchronize(dev)
         sc2.close()
+
+    # one untimed warm-up of the create/destroy path (the first scene teardown of a process costs ~0.7 s of
+    # one-time driver work), at 1 spp
+    e2e_step(scene.make_params(W, H, 1, sample_begin=rank, sample_end=rank + 1, spp_total=spp_total,
+                               max_depth=MAX_DEPTH, seed=95, mode=args.mode))
+    barrier()
+    e2e_steps = max(1, min(args.steps, 3))
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step(params)
     barrier()
     e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
     if world > 1:
@@ -313,6 +320,16 @@ def run_ours(args, rank, world, local_rank):
         except Exception:
             hbm_peak = None
         hbm_bytes = W * H * 12.0 + h2d  # accumulation write + scene read once
+        # DRAM traffic of one launch of this workload from the committed ncu --set full capture (null when the
+        # workload differs from the captured one)
+        traffic = None
+        try:
+            tj = json.load(open(os.path.join(REPO, "profiles", "r01_cta_v4_traffic.json")))
+            m = tj["match"]
+            if (m["scene"], m["width"], m["height"], m["spp_per_gpu"], m["mode"]) == (args.scene, W, H, SPP, int(st.mode_used)):
+                traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
+        except Exception:
+            traffic = None
         line = {
             "metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
@@ -331,7 +348,7 @@ def run_ours(args, rank, world, local_rank):
                     "what": "rt_scene_create (H2D of all scene tables + host BVH build) + render + reduce + divide + D2H of the float frame, per step"},
             "gpu_launches": int(args.steps * st.launches),
             "roofline": {"bound": "fp32-issue", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                         "traffic": None,
+                         "traffic": traffic,
                          "note": KERNEL_NAMES.get(int(st.mode_used), "?") + "; achieved = algorithmic FP32 ops per ray (SURVEY 8d constants, counted on this BVH) "
                                  "x rays per launch / CUDA-event kernel time; peak = MEASURED lane-FFMA issue rate of this GPU "
                                  "(rt_measure_fp32_peak, 1 op per lane-slot), of measured",
