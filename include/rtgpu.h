@@ -297,6 +297,11 @@ int rt_render(RtScene* scene, const RtRenderParams* params, float* out_rgb_mean,
 int rt_resolve_rgb8(RtScene* scene, const float* rgb_mean, uint32_t width, uint32_t height,
                     uint8_t* out_rgb8);
 
+/* Writes an 8-bit RGB image (row 0 = top, as rt_resolve_rgb8 produces it) as a PNG file: what
+ * image::save_buffer(file_name, &buf, nx, ny, ColorType::Rgb8) does at src/main.rs:128.
+ * Host only (zlib deflate); RT_ERR_IO when the file cannot be written. */
+int rt_write_png(const char* path, const uint8_t* rgb8, uint32_t width, uint32_t height);
+
 /* FP32 issue-rate microbenchmark (dependent-free FFMA chains on every SM): returns measured
  * lane-FFMA/s — the measured denominator of the instruction-issue roofline. */
 int rt_measure_fp32_peak(int device, double* out_ffma_per_s, double* out_sm_mhz_effective);

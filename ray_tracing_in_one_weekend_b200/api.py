@@ -123,7 +123,7 @@ class RtStats(C.Structure):
 # every symbol include/rtgpu.h declares
 EXPORTED_SYMBOLS = [
     "rt_scene_create", "rt_scene_destroy", "rt_scene_bvh_info", "rt_closest_hit", "rt_closest_hit_device",
-    "rt_camera_get_rays", "rt_render_device", "rt_render", "rt_resolve_rgb8", "rt_measure_fp32_peak",
+    "rt_camera_get_rays", "rt_render_device", "rt_render", "rt_resolve_rgb8", "rt_write_png", "rt_measure_fp32_peak",
     "rt_last_error", "rt_host_scene_build", "rt_host_scene_flat", "rt_host_scene_destroy",
 ]
 
@@ -151,6 +151,7 @@ def load_library() -> C.CDLL:
     lib.rt_render_device.argtypes = [vp, C.POINTER(RtRenderParams), vp, vp, C.POINTER(RtStats)]
     lib.rt_render.argtypes = [vp, C.POINTER(RtRenderParams), vp, C.POINTER(RtStats)]
     lib.rt_resolve_rgb8.argtypes = [vp, vp, u32, u32, vp]
+    lib.rt_write_png.argtypes = [C.c_char_p, vp, u32, u32]
     lib.rt_measure_fp32_peak.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.rt_host_scene_build.argtypes = [C.c_char_p, C.c_float, C.c_char_p, C.POINTER(vp)]
     lib.rt_host_scene_flat.argtypes = [vp]
@@ -323,6 +324,13 @@ class Scene:
                                           C.c_void_p(stream_ptr) if stream_ptr else None,
                                           C.byref(st) if st is not None else None))
         return st
+
+    @staticmethod
+    def write_png(path: str, rgb8: np.ndarray) -> None:
+        """image::save_buffer (main.rs:128): (H,W,3) uint8, row 0 = top -> PNG file."""
+        rgb8 = np.ascontiguousarray(rgb8, dtype=np.uint8)
+        h, w = rgb8.shape[:2]
+        _check(load_library().rt_write_png(os.fsencode(path), _ptr(rgb8), w, h))
 
     def resolve_rgb8(self, mean: np.ndarray) -> np.ndarray:
         """powf(0.5), *255.99 as u8, vertical flip (main.rs:98-105,127). Returns (H,W,3) uint8, row 0 = top."""

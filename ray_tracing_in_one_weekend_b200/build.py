@@ -19,7 +19,7 @@ LIB = os.path.join(HERE, "librtgpu.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 CXX = os.environ.get("CXX", "g++")
 
-HOST_SRCS = ["scene_api.cpp", "demo_scene.cpp", "bvh_build.cpp"]
+HOST_SRCS = ["scene_api.cpp", "demo_scene.cpp", "bvh_build.cpp", "png_writer.cpp"]
 CUDA_SRCS = ["rtgpu.cu"]
 CTA_FEATURE_SETS = [0, 4, 8, 9, 11, 15]  # cta_inst.cu is compiled once per set (kernels_cta.cuh)
 HEADERS = ["scene_api.hpp", "bvh_build.hpp", "device_types.h", "rt_device.cuh", "kernels.cuh", "kernels_cta.cuh",
@@ -73,7 +73,7 @@ def build_all(force: bool = False, verbose: bool = False) -> str:
         with ThreadPoolExecutor(max_workers=min(len(jobs), os.cpu_count() or 4)) as ex:
             log.extend(ex.map(_run, jobs))
     if force or _stale(LIB, objs):
-        log.append(_run([NVCC, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"]))
+        log.append(_run([NVCC, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lz"]))
     out = "".join(log)
     if verbose and out:
         print(out)

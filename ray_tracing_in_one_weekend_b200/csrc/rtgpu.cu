@@ -21,6 +21,9 @@ static int fail(int code, const std::string& msg) {
     g_err = msg;
     return code;
 }
+namespace rtb {
+int fail_png(const std::string& msg) { return fail(RT_ERR_IO, msg); }  // png_writer.cpp
+}
 #define CU_TRY(expr)                                                                                        \
     do {                                                                                                    \
         cudaError_t e__ = (expr);                                                                           \

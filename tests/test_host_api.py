@@ -107,3 +107,30 @@ def test_product_does_not_route_through_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".h")):
                 txt = open(os.path.join(dp, f), errors="replace").read()
                 assert "liboracle" not in txt and "oracle_lib" not in txt and "orc_" not in txt, f
+
+
+def test_png_writer_round_trip(rtlib, tmp_path):
+    """rt_write_png replaces image::save_buffer (main.rs:128): decode the file by hand (signature, IHDR, one
+    zlib stream of filter-0 rows, CRCs) and compare the pixels."""
+    import struct
+    import zlib
+    a = (np.random.default_rng(1).random((37, 53, 3)) * 255).astype(np.uint8)
+    path = str(tmp_path / "out.png")
+    rtlib.Scene.write_png(path, a)
+    raw = open(path, "rb").read()
+    assert raw[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, chunks = 8, []
+    while pos < len(raw):
+        n, typ = struct.unpack(">I4s", raw[pos:pos + 8])
+        data = raw[pos + 8:pos + 8 + n]
+        assert struct.unpack(">I", raw[pos + 8 + n:pos + 12 + n])[0] == zlib.crc32(typ + data)
+        chunks.append((typ, data))
+        pos += 12 + n
+    assert [c[0] for c in chunks] == [b"IHDR", b"IDAT", b"IEND"]
+    assert struct.unpack(">IIBBBBB", chunks[0][1]) == (53, 37, 8, 2, 0, 0, 0)
+    rows = np.frombuffer(zlib.decompress(chunks[1][1]), np.uint8).reshape(37, 1 + 53 * 3)
+    assert not rows[:, 0].any()
+    assert np.array_equal(rows[:, 1:].reshape(37, 53, 3), a)
+    lib = rtlib.load_library()
+    assert lib.rt_write_png(b"/nonexistent_dir/x.png", a.ctypes.data_as(C.c_void_p), 53, 37) == -3
+    assert lib.rt_write_png(None, None, 0, 0) == -3
