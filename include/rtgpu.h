@@ -262,6 +262,10 @@ typedef struct RtRenderParams {
 } RtRenderParams;
 
 #define RT_RENDER_COUNTERS 1u /* also count BVH node visits / primitive tests (slower build of the kernels) */
+#define RT_RENDER_RUSSIAN_ROULETTE 2u /* OPT-IN estimator, outside the parity contract: after every scatter the
+                                         path survives with probability min(max_element(attenuation), 1) and its
+                                         throughput is divided by it (the reference has this commented out,
+                                         src/main.rs:49-53).  Same expectation, fewer rays per path, other noise. */
 
 typedef struct RtStats {
     uint64_t paths;        /* depth-0 ray_color calls == width*height*(sample_end-sample_begin) */

@@ -28,6 +28,7 @@ TEX_CONSTANT, TEX_CHECKER, TEX_PERLIN, TEX_IMAGE = range(4)
 SKY_GRADIENT, SKY_BLACK, SKY_ENVMAP, SKY_CONSTANT = range(4)
 MODE_AUTO, MODE_MEGAKERNEL, MODE_WAVEFRONT, MODE_CTA_WAVEFRONT = range(4)
 RENDER_COUNTERS = 1
+RENDER_RUSSIAN_ROULETTE = 2
 
 
 class RtError(RuntimeError):

@@ -124,11 +124,12 @@ __global__ void __launch_bounds__(MEGA_THREADS) k_render_mega(DeviceScene sc, Re
                         Ray scattered;
                         bool ok = shade(sc, m, ray, rec, rng, emitted, att, scattered);
                         sum = sum + beta * emitted;  // main.rs:47
+                        if (ok && (a.max_depth & DEPTH_RR_FLAG)) ok = russian_roulette(att, rng);
                         if (ok) {                    // main.rs:48-54
                             beta = beta * att;
                             ray = scattered;
                             depth++;
-                            if (depth > a.max_depth) alive = false;  // main.rs:40-42
+                            if (depth > (a.max_depth & ~DEPTH_RR_FLAG)) alive = false;  // main.rs:40-42
                         } else {
                             alive = false;
                         }
@@ -482,11 +483,12 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS) k_wf_shade(DeviceScene sc, W
                 Ray scattered;
                 bool ok = shade_cls<CLS>(sc, m, ray, rec, rng, emitted, att, scattered);
                 if (CLS == CLS_CLASSIC) add = beta * emitted;  // main.rs:47 (only Emission emits, material.rs:26-28)
+                if (ok && (f.max_depth & DEPTH_RR_FLAG)) ok = russian_roulette(att, rng);
                 if (ok) {                                      // main.rs:48-54
                     beta = beta * att;
                     ray = scattered;
                     depth++;
-                    alive = depth <= f.max_depth;  // main.rs:40-42
+                    alive = depth <= (f.max_depth & ~DEPTH_RR_FLAG);  // main.rs:40-42
                 }
             }
             if (add.x != 0.0f || add.y != 0.0f || add.z != 0.0f) {

@@ -97,11 +97,12 @@ RT_DEV void cta_shade_item(const DeviceScene& sc, const CtaArgs& a, const CtaPoo
         Ray scattered;
         bool ok = shade_cls<CLS>(sc, m, ray, rec, rng, emitted, att, scattered);
         if (CLS == CLS_CLASSIC) add = beta * emitted;  // main.rs:47 (only Emission emits, material.rs:26-28)
+        if (ok && (a.max_depth & DEPTH_RR_FLAG)) ok = russian_roulette(att, rng);
         if (ok) {                                      // main.rs:48-54
             beta = beta * att;
             ray = scattered;
             depth++;
-            alive = depth <= a.max_depth;  // main.rs:40-42
+            alive = depth <= (a.max_depth & ~DEPTH_RR_FLAG);  // main.rs:40-42
         }
     }
     if (add.x != 0.0f || add.y != 0.0f || add.z != 0.0f) {

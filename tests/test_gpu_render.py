@@ -135,3 +135,27 @@ def test_resolve_matches_reference_output_stage(rtlib, oracle):
     assert np.abs(got.astype(int) - want.astype(int)).max() <= 1  # powf differs by ulps between libm and CUDA
     assert got[19, 0].tolist() == [0, 0, 255]  # NaN -> 0, negative -> 0, saturate (flipped: row 0 -> last row)
     scene.close()
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("name,tol", [("sphere_scene", 0.006), ("cornell_box_solid", 0.02), ("pbr_ibl", 0.01)])
+def test_russian_roulette_is_unbiased(rtlib, name, tol, mode):
+    """Opt-in estimator (RT_RENDER_RUSSIAN_ROULETTE; the reference has it commented out, main.rs:49-53): same
+    expectation as the reference integrator — mean luminance within `tol`, clipped per-channel RMSE within the
+    seed-to-seed noise of the plain estimator — with fewer rays per path."""
+    rt = rtlib
+    w, h, spp = 96, 64, 1024
+    scene = rt.Scene.from_name(name, w / h, 0)
+    a, sa = scene.render(w, h, spp, mode=mode)
+    b, _ = scene.render(w, h, spp, mode=mode, seed=12345)
+    r, sr = scene.render(w, h, spp, mode=mode, flags=rt.RENDER_RUSSIAN_ROULETTE)
+    assert sr.paths == sa.paths and sr.rays < sa.rays
+    rel = abs(lum(r) - lum(a)) / lum(a)
+    cap = float(np.nanpercentile(a, 99.5))
+    ca, cb, cr = np.clip(a, 0, cap), np.clip(b, 0, cap), np.clip(r, 0, cap)
+    noise = np.sqrt(np.nanmean((ca - cb) ** 2, axis=(0, 1)))
+    rmse = np.sqrt(np.nanmean((cr - ca) ** 2, axis=(0, 1)))
+    print(f"{name}: rays/path {sa.rays / sa.paths:.3f} -> {sr.rays / sr.paths:.3f}; lum rel {rel:.4%}; rmse {rmse} noise {noise}")
+    assert rel <= tol
+    assert np.all(rmse <= 1.5 * noise + 1e-4)
+    scene.close()
