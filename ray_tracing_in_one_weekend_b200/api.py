@@ -29,6 +29,7 @@ SKY_GRADIENT, SKY_BLACK, SKY_ENVMAP, SKY_CONSTANT = range(4)
 MODE_AUTO, MODE_MEGAKERNEL, MODE_WAVEFRONT, MODE_CTA_WAVEFRONT = range(4)
 RENDER_COUNTERS = 1
 RENDER_RUSSIAN_ROULETTE = 2
+SCENE_GPU_BVH = 1
 
 
 class RtError(RuntimeError):
@@ -92,7 +93,8 @@ class RtFlatScene(C.Structure):
 
 class RtBvhInfo(C.Structure):
     _fields_ = [("n_nodes", C.c_uint32), ("n_world_prims", C.c_uint32), ("max_depth", C.c_uint32),
-                ("max_leaf_prims", C.c_uint32), ("sah_cost", C.c_float), ("node_bytes", C.c_uint32)]
+                ("max_leaf_prims", C.c_uint32), ("sah_cost", C.c_float), ("node_bytes", C.c_uint32),
+                ("builder", C.c_uint32), ("build_ms", C.c_float)]
 
 
 class RtHit(C.Structure):
@@ -123,7 +125,7 @@ class RtStats(C.Structure):
 
 # every symbol include/rtgpu.h declares
 EXPORTED_SYMBOLS = [
-    "rt_scene_create", "rt_scene_destroy", "rt_scene_bvh_info", "rt_closest_hit", "rt_closest_hit_device",
+    "rt_scene_create", "rt_scene_create_ex", "rt_scene_destroy", "rt_scene_bvh_info", "rt_closest_hit", "rt_closest_hit_device",
     "rt_camera_get_rays", "rt_render_device", "rt_render", "rt_resolve_rgb8", "rt_write_png", "rt_measure_fp32_peak",
     "rt_last_error", "rt_host_scene_build", "rt_host_scene_flat", "rt_host_scene_destroy",
 ]
@@ -143,6 +145,7 @@ def load_library() -> C.CDLL:
     vp, fp, u32, sz = C.c_void_p, C.POINTER(C.c_float), C.c_uint32, C.c_size_t
     lib.rt_last_error.restype = C.c_char_p
     lib.rt_scene_create.argtypes = [C.POINTER(RtFlatScene), C.c_int, C.POINTER(vp)]
+    lib.rt_scene_create_ex.argtypes = [C.POINTER(RtFlatScene), C.c_int, C.c_uint32, C.POINTER(vp)]
     lib.rt_scene_destroy.argtypes = [vp]
     lib.rt_scene_destroy.restype = None
     lib.rt_scene_bvh_info.argtypes = [vp, C.POINTER(RtBvhInfo)]
@@ -258,19 +261,22 @@ def pixel_center_uv(width: int, height: int) -> np.ndarray:
 class Scene:
     """Device scene handle (rt_scene_create). Requires a CUDA device."""
 
-    def __init__(self, flat_ptr, device: int = 0):
+    def __init__(self, flat_ptr, device: int = 0, flags: Optional[int] = None):
         self._lib = load_library()
         h = C.c_void_p()
-        _check(self._lib.rt_scene_create(flat_ptr, device, C.byref(h)))
+        if flags is None:
+            _check(self._lib.rt_scene_create(flat_ptr, device, C.byref(h)))
+        else:
+            _check(self._lib.rt_scene_create_ex(flat_ptr, device, flags, C.byref(h)))
         self._h = h
         self.device = device
         self.camera = RtCamera.from_buffer_copy(bytes(flat_ptr.contents.camera))
 
     @classmethod
-    def from_name(cls, name: str, aspect_ratio: float, device: int = 0) -> "Scene":
+    def from_name(cls, name: str, aspect_ratio: float, device: int = 0, flags: Optional[int] = None) -> "Scene":
         hs = HostScene(name, aspect_ratio)
         try:
-            return cls(hs.flat, device)
+            return cls(hs.flat, device, flags)
         finally:
             hs.close()
 

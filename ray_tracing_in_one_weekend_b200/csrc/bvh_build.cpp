@@ -276,20 +276,17 @@ struct Builder {
 
 }  // namespace
 
-void build_bvh4(const RtFlatScene& fs, uint32_t leaf_max, BvhBuildResult& out) {
-    out = BvhBuildResult();
-    if (leaf_max < 1) leaf_max = 1;
-    if (leaf_max > 16) leaf_max = 16;
-    // world primitives
-    std::vector<uint32_t> world;
+// World primitives (those without RT_PRIM_FLAG_BOUNDARY_ONLY), their reference bounds and the padded,
+// conservative bounds the BVH stores.  Shared by the host SAH builder and the GPU LBVH builder (gpu_bvh.cu).
+static void world_boxes(const RtFlatScene& fs, std::vector<uint32_t>& world, std::vector<B3>& ref, std::vector<B3>& boxes) {
+    world.clear();
     for (uint32_t i = 0; i < fs.n_prims; i++)
         if (!(fs.prims[i].flags & RT_PRIM_FLAG_BOUNDARY_ONLY)) world.push_back(i);
-    out.n_world_prims = (uint32_t)world.size();
     if (world.empty()) throw std::runtime_error("scene has no world primitives");
 
     // "compact" scene region for the sphere-test error bound: camera + boxes of primitives that are
     // not giants (extent <= 64 x median extent) — ray origins (camera, hit points) live there.
-    std::vector<B3> ref(world.size());
+    ref.resize(world.size());
     std::vector<float> ext(world.size());
     for (size_t k = 0; k < world.size(); k++) {
         ref[k] = box_to_world(fs, fs.prims[world[k]].xform, reference_bbox(fs, world[k]));
@@ -303,7 +300,7 @@ void build_bvh4(const RtFlatScene& fs, uint32_t leaf_max, BvhBuildResult& out) {
     for (size_t k = 0; k < world.size(); k++)
         if (ext[k] <= 64.0f * median_ext) compact.grow(ref[k]);
 
-    std::vector<B3> boxes(world.size());
+    boxes.resize(world.size());
     for (size_t k = 0; k < world.size(); k++) {
         const RtPrim& p = fs.prims[world[k]];
         B3 b = ref[k];
@@ -331,6 +328,30 @@ void build_bvh4(const RtFlatScene& fs, uint32_t leaf_max, BvhBuildResult& out) {
         pad_box(b, abs_pad);
         boxes[k] = b;
     }
+}
+
+void compute_world_boxes(const RtFlatScene& fs, std::vector<uint32_t>& world, std::vector<Box6>& ref_out, std::vector<Box6>& padded_out) {
+    std::vector<B3> ref, boxes;
+    world_boxes(fs, world, ref, boxes);
+    ref_out.resize(world.size());
+    padded_out.resize(world.size());
+    for (size_t k = 0; k < world.size(); k++)
+        for (int a = 0; a < 3; a++) {
+            ref_out[k].lo[a] = ref[k].lo[a];
+            ref_out[k].hi[a] = ref[k].hi[a];
+            padded_out[k].lo[a] = boxes[k].lo[a];
+            padded_out[k].hi[a] = boxes[k].hi[a];
+        }
+}
+
+void build_bvh4(const RtFlatScene& fs, uint32_t leaf_max, BvhBuildResult& out) {
+    out = BvhBuildResult();
+    if (leaf_max < 1) leaf_max = 1;
+    if (leaf_max > 16) leaf_max = 16;
+    std::vector<uint32_t> world;
+    std::vector<B3> ref, boxes;
+    world_boxes(fs, world, ref, boxes);
+    out.n_world_prims = (uint32_t)world.size();
 
     Builder bl{boxes, {}, {}, out.nodes, out.leaf_order, leaf_max};
     bl.cen.resize(3 * world.size());

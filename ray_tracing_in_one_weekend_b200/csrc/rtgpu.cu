@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "bvh_build.hpp"
+#include "gpu_bvh.hpp"
 #include "kernels.cuh"
 #include "kernels_cta.cuh"
 #include "scene_api.hpp"
@@ -238,21 +239,19 @@ extern "C" {
 const char* rt_last_error(void) { return g_err.c_str(); }
 
 int rt_scene_create(const RtFlatScene* desc, int device, RtScene** out) {
+    return rt_scene_create_ex(desc, device, (uint32_t)env_int("RT_SCENE_FLAGS", 0), out);
+}
+
+int rt_scene_create_ex(const RtFlatScene* desc, int device, uint32_t flags, RtScene** out) {
     if (!out) return fail(RT_ERR_ARG, "out is NULL");
     *out = nullptr;
+    if (flags & ~RT_SCENE_GPU_BVH) return fail(RT_ERR_ARG, "unknown scene flag");
     std::string why = validate(desc);
     if (!why.empty()) return fail(RT_ERR_ARG, why);
     int n_dev = 0;
     CU_TRY(cudaGetDeviceCount(&n_dev));
     if (device < 0 || device >= n_dev) return fail(RT_ERR_CUDA, "no such CUDA device");
     CU_TRY(cudaSetDevice(device));
-
-    BvhBuildResult bvh;
-    try {
-        build_bvh4(*desc, (uint32_t)env_int("RT_LEAF_MAX", 1), bvh);
-    } catch (const std::exception& e) {
-        return fail(RT_ERR_ARG, e.what());
-    }
 
     std::unique_ptr<RtScene> s(new RtScene());
     s->device = device;
@@ -262,6 +261,38 @@ int rt_scene_create(const RtFlatScene* desc, int device, RtScene** out) {
     cudaDeviceProp prop;
     CU_TRY(cudaGetDeviceProperties(&prop, device));
     s->sm_count = prop.multiProcessorCount;
+
+    // acceleration structure: host SAH builder (default) or the GPU LBVH builder
+    BvhBuildResult bvh;
+    const BvhNode4* gpu_nodes = nullptr;
+    uint32_t builder = 0;
+    float build_ms = 0.0f;
+    auto b0 = std::chrono::steady_clock::now();
+    if (flags & RT_SCENE_GPU_BVH) {
+        GpuBvhResult g;
+        std::string err;
+        if (!gpu_build_bvh4(*desc, s->stream, g, err)) return fail(RT_ERR_CUDA, "GPU BVH build: " + err);
+        if (g.max_depth * 3u + 4u <= (uint32_t)STACK_SIZE) {
+            s->allocs.push_back(g.nodes);
+            gpu_nodes = g.nodes;
+            bvh.leaf_order = std::move(g.leaf_order);
+            bvh.n_world_prims = g.n_world_prims;
+            bvh.max_depth = g.max_depth;
+            bvh.max_leaf_prims = 1;
+            bvh.nodes.resize(g.n_nodes);  // sizes only; the nodes already live on the device
+            builder = 1;
+        } else {
+            cudaFree(g.nodes);  // degenerate Morton tree, too deep for the traversal stack: use the SAH builder
+        }
+    }
+    if (builder == 0) {
+        try {
+            build_bvh4(*desc, (uint32_t)env_int("RT_LEAF_MAX", 1), bvh);
+        } catch (const std::exception& e) {
+            return fail(RT_ERR_ARG, e.what());
+        }
+    }
+    build_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - b0).count();
 
     // device primitive array: world primitives in BVH leaf order, then boundary-only primitives in flat order
     std::vector<uint32_t> order = bvh.leaf_order;
@@ -313,7 +344,8 @@ int rt_scene_create(const RtFlatScene* desc, int device, RtScene** out) {
         const RtTexture& t = desc->textures[i];
         texs[i] = DevTexture{t.kind, t.a, t.b, 0, t.p[0], t.p[1], t.p[2], t.p[3]};
     }
-    CU_TRY(upload(s.get(), bvh.nodes.data(), bvh.nodes.size(), &s->ds.nodes));
+    if (gpu_nodes) s->ds.nodes = gpu_nodes;
+    else CU_TRY(upload(s.get(), bvh.nodes.data(), bvh.nodes.size(), &s->ds.nodes));
     CU_TRY(upload(s.get(), prims.data(), prims.size(), &s->ds.prims));
     CU_TRY(upload(s.get(), motion.data(), motion.size(), &s->ds.motion));
     CU_TRY(upload(s.get(), ops.data(), ops.size(), &s->ds.ops));
@@ -391,7 +423,7 @@ int rt_scene_create(const RtFlatScene* desc, int device, RtScene** out) {
         if (p.kind == RT_PRIM_XYRECT || p.kind == RT_PRIM_XZRECT || p.kind == RT_PRIM_YZRECT) s->features |= F_RECT;
     }
     s->camera = c;
-    s->bvh = RtBvhInfo{(uint32_t)bvh.nodes.size(), bvh.n_world_prims, bvh.max_depth, bvh.max_leaf_prims, bvh.sah_cost, (uint32_t)sizeof(BvhNode4)};
+    s->bvh = RtBvhInfo{(uint32_t)bvh.nodes.size(), bvh.n_world_prims, bvh.max_depth, bvh.max_leaf_prims, bvh.sah_cost, (uint32_t)sizeof(BvhNode4), builder, build_ms};
     if (bvh.max_depth * 3u + 4u > (uint32_t)STACK_SIZE) return fail(RT_ERR_UNSUPPORTED, "BVH too deep for the traversal stack");
 
     void* p = nullptr;
@@ -982,7 +1014,7 @@ int rt_test_bvh_validate(const RtFlatScene* desc, uint32_t leaf_max, RtBvhInfo* 
         int want = (desc->prims[i].flags & RT_PRIM_FLAG_BOUNDARY_ONLY) ? 0 : 1;
         if (seen[i] != want) return fail(RT_ERR_ARG, "bvh: primitive referenced " + std::to_string(seen[i]) + " times");
     }
-    if (info) *info = RtBvhInfo{(uint32_t)bvh.nodes.size(), bvh.n_world_prims, bvh.max_depth, bvh.max_leaf_prims, bvh.sah_cost, (uint32_t)sizeof(BvhNode4)};
+    if (info) *info = RtBvhInfo{(uint32_t)bvh.nodes.size(), bvh.n_world_prims, bvh.max_depth, bvh.max_leaf_prims, bvh.sah_cost, (uint32_t)sizeof(BvhNode4), 0u, 0.0f};
     return RT_OK;
 }
 
