@@ -198,7 +198,8 @@ typedef struct RtFlatScene {
 typedef struct RtScene RtScene; /* opaque: owns device memory, texture objects, streams */
 
 /* Uploads `desc` to CUDA device `device` (copies everything; the caller may free `desc` on return),
- * builds the SAH 4-wide BVH (128-byte, 32-byte-aligned nodes) over the world primitives.
+ * builds the 4-wide BVH (128-byte, 32-byte-aligned nodes) over the world primitives: binned SAH on the host
+ * below 32768 world primitives, LBVH on the device from there on (see rt_scene_create_ex).
  * Replaces: the scene hand-off `let (world, cam) = scene_fn(aspect)` + `build_bvh`
  * (src/main.rs:74, src/demo_scene.rs:223-227, src/hitable.rs:177-221). */
 int rt_scene_create(const RtFlatScene* desc, int device, RtScene** out);
