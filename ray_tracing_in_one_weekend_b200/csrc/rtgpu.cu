@@ -263,15 +263,22 @@ int rt_scene_create_ex(const RtFlatScene* desc, int device, uint32_t flags, RtSc
     if (device < 0 || device >= n_dev) return fail(RT_ERR_CUDA, "no such CUDA device");
     CU_TRY(cudaSetDevice(device));
 
+    const bool timing = std::getenv("RT_TIMING") != nullptr;  // development aid: stage times on stderr
+    auto t_prev = std::chrono::steady_clock::now();
+    auto stage = [&](const char* what) {
+        if (!timing) return;
+        auto now = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[rt_scene_create] %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(now - t_prev).count());
+        t_prev = now;
+    };
     std::unique_ptr<RtScene> s(new RtScene());
     s->device = device;
     CU_TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     CU_TRY(cudaEventCreate(&s->ev0));
     CU_TRY(cudaEventCreate(&s->ev1));
-    cudaDeviceProp prop;
-    CU_TRY(cudaGetDeviceProperties(&prop, device));
-    s->sm_count = prop.multiProcessorCount;
+    CU_TRY(cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device));  // (cudaGetDeviceProperties costs milliseconds)
 
+    stage("stream/events/attrs");
     // acceleration structure: host SAH builder (default) or the GPU LBVH builder
     BvhBuildResult bvh;
     const BvhNode4* gpu_nodes = nullptr;
@@ -303,6 +310,7 @@ int rt_scene_create_ex(const RtFlatScene* desc, int device, uint32_t flags, RtSc
         }
     }
     build_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - b0).count();
+    stage("bvh build");
 
     // device primitive array: world primitives in BVH leaf order, then boundary-only primitives in flat order
     std::vector<uint32_t> order = bvh.leaf_order;
@@ -354,6 +362,7 @@ int rt_scene_create_ex(const RtFlatScene* desc, int device, uint32_t flags, RtSc
         const RtTexture& t = desc->textures[i];
         texs[i] = DevTexture{t.kind, t.a, t.b, 0, t.p[0], t.p[1], t.p[2], t.p[3]};
     }
+    stage("host packing");
     if (gpu_nodes) s->ds.nodes = gpu_nodes;
     else CU_TRY(upload(s.get(), bvh.nodes.data(), bvh.nodes.size(), &s->ds.nodes));
     CU_TRY(upload(s.get(), prims.data(), prims.size(), &s->ds.prims));
@@ -363,6 +372,7 @@ int rt_scene_create_ex(const RtFlatScene* desc, int device, uint32_t flags, RtSc
     CU_TRY(upload(s.get(), mats.data(), mats.size(), &s->ds.mats));
     CU_TRY(upload(s.get(), texs.data(), texs.size(), &s->ds.texs));
 
+    stage("table uploads");
     // Perlin tables: gradients behind a texture object (texel fetch), permutations as bytes
     {
         std::vector<float4> grad(std::max<size_t>(1, (size_t)desc->n_perlin * 256));
@@ -418,6 +428,7 @@ int rt_scene_create_ex(const RtFlatScene* desc, int device, uint32_t flags, RtSc
         }
         CU_TRY(upload(s.get(), imgs.data(), imgs.size(), &s->ds.images));
     }
+    stage("perlin + images");
     s->ds.sky = DevSky{desc->sky.kind, desc->sky.image, desc->sky.color[0], desc->sky.color[1], desc->sky.color[2]};
     const RtCamera& c = desc->camera;
     auto v3 = [](const float* p) { return V3f{p[0], p[1], p[2]}; };
@@ -456,6 +467,7 @@ int rt_scene_create_ex(const RtFlatScene* desc, int device, uint32_t flags, RtSc
     }
     if (s->mega_blocks_per_sm < 1 || s->mega_blocks_per_sm_cnt < 1) return fail(RT_ERR_CUDA, "render kernel does not fit on an SM");
     CU_TRY(cudaDeviceSynchronize());
+    stage("scratch + occupancy + sync");
     *out = s.release();
     return RT_OK;
 }
