@@ -25,7 +25,11 @@ for l in (r.stdout + r.stderr).splitlines():
         print(l.strip()); want = False
     elif "spill" in l and locals().get("want"):
         print(l.strip(), end=" | ")
-objs = [os.path.join(b.CSRC, s.replace(".cpp", ".o")) for s in b.HOST_SRCS] + [obj]
-subprocess.check_call([b.NVCC, "-shared", "-o", os.path.join(out, "librtgpu.so")] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"])
+objs = [os.path.join(b.CSRC, s.replace(".cpp", ".o")) for s in b.HOST_SRCS] + [obj, os.path.join(b.CSRC, "gpu_bvh.o")]
+for f in b.CTA_FEATURE_SETS:  # the CTA renderer lives in its own translation units
+    o = os.path.join(os.path.abspath(out), f"cta_f{f}.o")
+    subprocess.check_call([b.NVCC] + [x for x in b.NVCC_FLAGS if x not in ("-Xptxas", "-v")] + extra + [f"-DRT_CTA_F={f}", "-c", "cta_inst.cu", "-o", o], cwd=b.CSRC)
+    objs.append(o)
+subprocess.check_call([b.NVCC, "-shared", "-o", os.path.join(out, "librtgpu.so")] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lz"])
 os.remove(obj)
 print(os.path.join(out, "librtgpu.so"))
