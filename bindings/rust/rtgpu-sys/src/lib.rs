@@ -38,6 +38,7 @@ pub enum RtScene {}
 
 extern "C" {
     pub fn rt_scene_create(desc: *const RtFlatScene, device: c_int, out: *mut *mut RtScene) -> c_int;
+    pub fn rt_scene_create_ex(desc: *const RtFlatScene, device: c_int, flags: u32, out: *mut *mut RtScene) -> c_int; // RT_SCENE_GPU_BVH = 1
     pub fn rt_scene_destroy(scene: *mut RtScene);
     pub fn rt_closest_hit(scene: *mut RtScene, o_xyz: *const f32, d_xyz: *const f32, times: *const f32, n: usize,
                           t_min: f32, t_max: f32, out: *mut RtHit) -> c_int;
@@ -45,5 +46,6 @@ extern "C" {
     pub fn rt_render_device(scene: *mut RtScene, params: *const RtRenderParams, accum_sum_rgb: *mut f32,
                             cuda_stream: *mut c_void, stats: *mut RtStats) -> c_int;
     pub fn rt_resolve_rgb8(scene: *mut RtScene, rgb_mean: *const f32, width: u32, height: u32, out_rgb8: *mut u8) -> c_int;
+    pub fn rt_write_png(path: *const c_char, rgb8: *const u8, width: u32, height: u32) -> c_int;
     pub fn rt_last_error() -> *const c_char;
 }
