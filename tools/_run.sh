@@ -1,2 +1,2 @@
-for s in sphere_scene cover_100k_motion cornell_box final_scene; do for l in ray_tracing_in_one_weekend_b200/librtgpu.so variants/maj/librtgpu.so; do echo "== $l"; RTGPU_LIB=$l timeout 300 python tools/mode_sweep.py $s 1920 1080 32 3 2>&1 | tail -1; done; done
-RTGPU_LIB=variants/maj/librtgpu.so timeout 600 python -m pytest tests/test_gpu_render.py -m gpu -x -q -k "cta_wavefront or agree" 2>&1 | tail -2
+timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/c31_pytest.log 2>&1; tail -2 gpurun_out/c31_pytest.log
+for s in sphere_scene cover_100k_motion; do timeout 300 python tools/mode_sweep.py $s 1920 1080 32 3 2>&1 | tail -1; done
