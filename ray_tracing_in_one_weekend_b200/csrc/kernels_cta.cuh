@@ -31,6 +31,9 @@ namespace rtb {
 #ifndef RT_CTA_MIN_BLOCKS
 #define RT_CTA_MIN_BLOCKS 2  // register cap 85 (80 used): fits traversal and the common shading classes
 #endif
+#ifndef RT_CTA_PROFILE
+#define RT_CTA_PROFILE 0  // development: phase / work cycle counters into stats[8..13] (class_counts of RtStats)
+#endif
 constexpr int CTA_THREADS = RT_CTA_THREADS;
 constexpr int CTA_WARPS = CTA_THREADS / 32;
 constexpr int CTA_MIN_BLOCKS = RT_CTA_MIN_BLOCKS;
@@ -217,6 +220,11 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
     }
     __syncthreads();
 
+#if RT_CTA_PROFILE
+    long long pf_phase[4] = {0, 0, 0, 0};  // thread 0: wall cycles of D+regen, traverse, shade (incl. barrier waits), iterations
+    long long pf_work[2] = {0, 0};         // lane 0 of every warp: own work cycles in traverse, shade
+    long long pf_t = clock64();
+#endif
     for (;;) {
         // ================================================================== D: regenerate ended paths
         if (tid == 0) {
@@ -269,6 +277,9 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
             P.todo[n_surv + i] = (uint16_t)pid;  // consecutive pixels of a row sit next to each other
         }
         __syncthreads();
+#if RT_CTA_PROFILE
+        { long long t = clock64(); if (tid == 0) { pf_phase[0] += t - pf_t; pf_phase[3]++; } pf_t = t; }
+#endif
 
         // ================================================================== A: traverse (one ray per lane)
         {
@@ -332,7 +343,13 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
                 __syncwarp();
             }
         }
+#if RT_CTA_PROFILE
+        if (lane == 0) pf_work[0] += clock64() - pf_t;
+#endif
         __syncthreads();
+#if RT_CTA_PROFILE
+        { long long t = clock64(); if (tid == 0) pf_phase[1] += t - pf_t; pf_t = t; }
+#endif
 
         // ================================================================== C: shade, class by class
         {
@@ -375,8 +392,26 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
                 __syncwarp();
             }
         }
+#if RT_CTA_PROFILE
+        if (lane == 0) pf_work[1] += clock64() - pf_t;
+#endif
         __syncthreads();
+#if RT_CTA_PROFILE
+        { long long t = clock64(); if (tid == 0) pf_phase[2] += t - pf_t; pf_t = t; }
+#endif
     }
+#if RT_CTA_PROFILE
+    if (tid == 0) {
+        atomicAdd(a.stats + 8, (unsigned long long)pf_phase[0]);
+        atomicAdd(a.stats + 9, (unsigned long long)pf_phase[1]);
+        atomicAdd(a.stats + 10, (unsigned long long)pf_phase[2]);
+        atomicAdd(a.stats + 11, (unsigned long long)pf_phase[3]);
+    }
+    if (lane == 0) {
+        atomicAdd(a.stats + 12, (unsigned long long)pf_work[0]);
+        atomicAdd(a.stats + 13, (unsigned long long)pf_work[1]);
+    }
+#endif
 
     const unsigned long long rays = warp_sum_u64(n_rays), shades = warp_sum_u64(n_shade);
     if (lane == 0) {
