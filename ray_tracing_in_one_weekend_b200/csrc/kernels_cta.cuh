@@ -1,25 +1,30 @@
 // CTA-local wavefront renderer (sm_100a): the whole wavefront loop runs INSIDE one persistent kernel.
 //
-// Every thread block owns a pool of N paths in shared memory (64 B of path state + 16 B of queue space per
-// path, e.g. 768 paths = 60 KB, three blocks per SM out of Blackwell's 227 KB) and iterates, separated by
-// __syncthreads():
+// Every thread block (384 threads, two blocks per SM) owns a pool of N = 1152 paths in shared memory (64 B of
+// path state + 18 B of queue space per path = 92 KB per block out of Blackwell's 227 KB per SM) and iterates,
+// separated by __syncthreads():
 //
 //   D  regenerate   one 64-bit atomicAdd per block and iteration reserves path indices for every path that
-//                   ended; threads generate the new camera rays (main.rs:88-93) into the dead slots
-//   A  traverse     warps pull path ids from a shared-memory counter, one ray per lane, while-while BVH
-//                   traversal (rt_device.cuh); a lane that finishes writes (t, prim) back and appends the path
-//                   to the shared-memory queue of its SHADING CLASS; idle lanes are refilled from the counter
-//                   as soon as `refill_idle` lanes of the warp are idle (shared-memory atomics make this cheap)
-//   C  shade        threads walk the class queues in class order (every class range padded to a warp
-//                   multiple, so a warp runs ONE material group): sky / emitted / scatter
-//                   (material.rs, pbr.rs, texture.rs), radiance to the frame with red.global.add.f32, the
-//                   scattered ray back into the slot, or the slot onto the dead list
+//                   ended; threads generate the new camera rays (main.rs:88-93) into the dead slots and append
+//                   them to the TODO list in path-index order (32 neighbouring pixels of a row per warp)
+//   A  traverse     A2: scattered rays first — warps pull todo entries from a shared-memory counter, one ray
+//                   per lane, while-while BVH traversal (rt_device.cuh); idle lanes are refilled from the
+//                   counter as soon as `refill_idle` lanes of the warp are idle.  A1: then the camera rays, a
+//                   coherent warp of 32 at a time, run to completion (uniform chunks that fill the tail).
+//                   A lane that finishes writes (t, prim) back and appends the path to the shared-memory
+//                   queue of its SHADING CLASS
+//   C  shade        warps pull 32-entry chunks of the class queues from a counter, most expensive class
+//                   first (every class range padded to a warp multiple, so a warp runs ONE material group):
+//                   sky / emitted / scatter (material.rs, pbr.rs, texture.rs), radiance to the frame with
+//                   red.global.add.f32, the scattered ray back into the slot and onto the todo list, or the
+//                   slot onto the dead list
 //
 // Nothing but the scene (L1-resident), the accumulation atomics and one counter atomic per block-iteration
 // touches global memory: no path-state traffic, no global queues, no kernel boundaries, no grid-wide tail
-// until the frame itself drains.  Blocks are independent; 2-3 resident blocks per SM fill each other's
+// until the frame itself drains.  Blocks are independent; the two resident blocks of an SM fill each other's
 // barrier waits.  Replaces main.rs:38-60,84-97 with the same device functions and RNG streams as the other
 // two renderers (a path's stream depends only on (seed, pixel, global sample index)).
+// One translation unit per scene feature set instantiates the kernel (cta_inst.cu).
 #pragma once
 #include "rt_device.cuh"
 
