@@ -1,2 +1,6 @@
-timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/c31_pytest.log 2>&1; tail -2 gpurun_out/c31_pytest.log
-for s in sphere_scene cover_100k_motion; do timeout 300 python tools/mode_sweep.py $s 1920 1080 32 3 2>&1 | tail -1; done
+run() { echo "== $1 $2"; RTGPU_LIB=$1 timeout 300 python tools/mode_sweep.py $2 1920 1080 32 3 2>&1 | tail -1; }
+for sc in sphere_scene simple_light_scene; do
+run ray_tracing_in_one_weekend_b200/librtgpu.so $sc
+run variants/pu2/librtgpu.so $sc
+run variants/pu7/librtgpu.so $sc
+done
