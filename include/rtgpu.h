@@ -273,6 +273,10 @@ typedef struct RtRenderParams {
 } RtRenderParams;
 
 #define RT_RENDER_COUNTERS 1u /* also count BVH node visits / primitive tests (slower build of the kernels) */
+#define RT_RENDER_COSINE_SAMPLING 4u /* OPT-IN estimator, outside the parity contract: Lambert and every pbr.rs
+                                        material draw the scattered direction cosine-weighted (pdf cos/pi) instead
+                                        of uniformly on the hemisphere (src/material.rs:52-59, src/pbr.rs) and
+                                        re-weight by 1/(2 cos).  Same expectation, less variance. */
 #define RT_RENDER_RUSSIAN_ROULETTE 2u /* OPT-IN estimator, outside the parity contract: after every scatter the
                                          path survives with probability min(max_element(attenuation), 1) and its
                                          throughput is divided by it (the reference has this commented out,

@@ -6,5 +6,5 @@ thin ctypes mirror used by tests and bench.py.  No CPU fallback exists.
 from .api import (  # noqa: F401
     HostScene, Scene, RtError, RtRenderParams, RtStats, RtFlatScene, RtCamera, HIT_DTYPE, load_library,
     camera_get_rays, pixel_center_uv, flat_to_numpy, measure_fp32_peak, LIB_PATH, ASSET_DIR, EXPORTED_SYMBOLS,
-    MODE_AUTO, MODE_MEGAKERNEL, MODE_WAVEFRONT, MODE_CTA_WAVEFRONT, RENDER_COUNTERS, RENDER_RUSSIAN_ROULETTE, SCENE_GPU_BVH,
+    MODE_AUTO, MODE_MEGAKERNEL, MODE_WAVEFRONT, MODE_CTA_WAVEFRONT, RENDER_COUNTERS, RENDER_RUSSIAN_ROULETTE, RENDER_COSINE_SAMPLING, SCENE_GPU_BVH,
 )

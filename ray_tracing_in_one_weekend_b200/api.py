@@ -29,6 +29,7 @@ SKY_GRADIENT, SKY_BLACK, SKY_ENVMAP, SKY_CONSTANT = range(4)
 MODE_AUTO, MODE_MEGAKERNEL, MODE_WAVEFRONT, MODE_CTA_WAVEFRONT = range(4)
 RENDER_COUNTERS = 1
 RENDER_RUSSIAN_ROULETTE = 2
+RENDER_COSINE_SAMPLING = 4
 SCENE_GPU_BVH = 1
 
 

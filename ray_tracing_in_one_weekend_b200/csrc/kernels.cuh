@@ -122,14 +122,14 @@ __global__ void __launch_bounds__(MEGA_THREADS) k_render_mega(DeviceScene sc, Re
                         HitRec rec = fill_hit<F>(sc, ray, h.prim, h.t, (m.reserved & 1u) != 0u);
                         V3f emitted, att;
                         Ray scattered;
-                        bool ok = shade(sc, m, ray, rec, rng, emitted, att, scattered);
+                        bool ok = shade(sc, m, ray, rec, rng, emitted, att, scattered, (a.max_depth & DEPTH_COS_FLAG) != 0u);
                         sum = sum + beta * emitted;  // main.rs:47
                         if (ok && (a.max_depth & DEPTH_RR_FLAG)) ok = russian_roulette(att, rng);
                         if (ok) {                    // main.rs:48-54
                             beta = beta * att;
                             ray = scattered;
                             depth++;
-                            if (depth > (a.max_depth & ~DEPTH_RR_FLAG)) alive = false;  // main.rs:40-42
+                            if (depth > (a.max_depth & DEPTH_MASK)) alive = false;  // main.rs:40-42
                         } else {
                             alive = false;
                         }
@@ -481,14 +481,14 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS) k_wf_shade(DeviceScene sc, W
                 HitRec rec = fill_hit<F>(sc, ray, ht.y, __uint_as_float(ht.x), want_uv);
                 V3f emitted, att;
                 Ray scattered;
-                bool ok = shade_cls<CLS>(sc, m, ray, rec, rng, emitted, att, scattered);
+                bool ok = shade_cls<CLS>(sc, m, ray, rec, rng, emitted, att, scattered, (f.max_depth & DEPTH_COS_FLAG) != 0u);
                 if (CLS == CLS_CLASSIC) add = beta * emitted;  // main.rs:47 (only Emission emits, material.rs:26-28)
                 if (ok && (f.max_depth & DEPTH_RR_FLAG)) ok = russian_roulette(att, rng);
                 if (ok) {                                      // main.rs:48-54
                     beta = beta * att;
                     ray = scattered;
                     depth++;
-                    alive = depth <= (f.max_depth & ~DEPTH_RR_FLAG);  // main.rs:40-42
+                    alive = depth <= (f.max_depth & DEPTH_MASK);  // main.rs:40-42
                 }
             }
             if (add.x != 0.0f || add.y != 0.0f || add.z != 0.0f) {

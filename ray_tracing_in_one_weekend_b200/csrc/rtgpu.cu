@@ -664,7 +664,8 @@ static int render_wavefront(RtScene* s, const RtRenderParams* rp, float* accum, 
     f.height = rp->height;
     f.s_begin = rp->sample_begin;
     f.n_samples = rp->sample_end - rp->sample_begin;
-    f.max_depth = rp->max_depth | ((rp->flags & RT_RENDER_RUSSIAN_ROULETTE) ? DEPTH_RR_FLAG : 0u);
+    f.max_depth = rp->max_depth | ((rp->flags & RT_RENDER_RUSSIAN_ROULETTE) ? DEPTH_RR_FLAG : 0u) |
+                  ((rp->flags & RT_RENDER_COSINE_SAMPLING) ? DEPTH_COS_FLAG : 0u);
     f.refill_threshold = (uint32_t)env_int("RT_WF_REFILL", 24);
     f.chunk = wf_chunk();
     f.seed = rp->seed;
@@ -702,7 +703,7 @@ int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* c
     if (!s || !rp || !accum) return fail(RT_ERR_ARG, "NULL argument");
     if (rp->width == 0 || rp->height == 0 || rp->sample_end < rp->sample_begin) return fail(RT_ERR_ARG, "bad render params");
     if (rp->mode > RT_MODE_CTA_WAVEFRONT) return fail(RT_ERR_ARG, "bad render mode");
-    if (rp->max_depth >= DEPTH_RR_FLAG) return fail(RT_ERR_ARG, "max_depth too large");
+    if (rp->max_depth > DEPTH_MASK) return fail(RT_ERR_ARG, "max_depth too large");
     uint32_t mode = rp->mode;
     if (mode == RT_MODE_AUTO) mode = (uint32_t)env_int("RT_DEFAULT_MODE", RT_MODE_CTA_WAVEFRONT);
     if (mode == RT_MODE_CTA_WAVEFRONT && rp->sample_end > rp->sample_begin) {
@@ -720,7 +721,8 @@ int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* c
         a.width = rp->width;
         a.height = rp->height;
         a.s_begin = rp->sample_begin;
-        a.max_depth = rp->max_depth | ((rp->flags & RT_RENDER_RUSSIAN_ROULETTE) ? DEPTH_RR_FLAG : 0u);
+        a.max_depth = rp->max_depth | ((rp->flags & RT_RENDER_RUSSIAN_ROULETTE) ? DEPTH_RR_FLAG : 0u) |
+                  ((rp->flags & RT_RENDER_COSINE_SAMPLING) ? DEPTH_COS_FLAG : 0u);
         a.per_sample = rp->width * rp->height;
         a.total_paths = (unsigned long long)a.per_sample * (rp->sample_end - rp->sample_begin);
         a.n_paths = (uint32_t)std::max(32, std::min(4096, env_int("RT_CTA_PATHS", 3 * CTA_THREADS))) & ~31u;
@@ -801,7 +803,8 @@ int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* c
     a.height = rp->height;
     a.s_begin = rp->sample_begin;
     a.s_end = rp->sample_end;
-    a.max_depth = rp->max_depth | ((rp->flags & RT_RENDER_RUSSIAN_ROULETTE) ? DEPTH_RR_FLAG : 0u);
+    a.max_depth = rp->max_depth | ((rp->flags & RT_RENDER_RUSSIAN_ROULETTE) ? DEPTH_RR_FLAG : 0u) |
+                  ((rp->flags & RT_RENDER_COSINE_SAMPLING) ? DEPTH_COS_FLAG : 0u);
     a.tiles_x = (rp->width + 7) / 8;
     a.n_tiles = a.tiles_x * ((rp->height + 3) / 4);
     a.seed = rp->seed;

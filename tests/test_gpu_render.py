@@ -159,3 +159,27 @@ def test_russian_roulette_is_unbiased(rtlib, name, tol, mode):
     assert rel <= tol
     assert np.all(rmse <= 1.5 * noise + 1e-4)
     scene.close()
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("name,tol", [("pbr_ibl", 0.01), ("test_sphere", 0.006), ("furnace_disney_metal", 0.02)])
+def test_cosine_sampling_is_unbiased(rtlib, name, tol, mode):
+    """Opt-in estimator (RT_RENDER_COSINE_SAMPLING): Lambert (test_sphere) and the pbr.rs materials draw
+    cosine-weighted directions and re-weight by 1/(2 cos) — same expectation as the reference's uniform-hemisphere
+    estimator (mean luminance within `tol`, clipped RMSE within the plain estimator's seed-to-seed noise)."""
+    rt = rtlib
+    w, h, spp = (96, 64, 1024) if not name.startswith("furnace") else (16, 16, 8192)
+    scene = rt.Scene.from_name(name, w / h, 0)
+    a, sa = scene.render(w, h, spp, mode=mode)
+    b, _ = scene.render(w, h, spp, mode=mode, seed=12345)
+    c, sc = scene.render(w, h, spp, mode=mode, flags=rt.RENDER_COSINE_SAMPLING)
+    assert sc.paths == sa.paths
+    rel = abs(lum(c) - lum(a)) / lum(a)
+    cap = float(np.nanpercentile(a, 99.5))
+    ca, cb, cc = np.clip(a, 0, cap), np.clip(b, 0, cap), np.clip(c, 0, cap)
+    noise = np.sqrt(np.nanmean((ca - cb) ** 2, axis=(0, 1)))
+    rmse = np.sqrt(np.nanmean((cc - ca) ** 2, axis=(0, 1)))
+    print(f"{name}: lum rel {rel:.4%}; rmse {rmse} plain noise {noise}")
+    assert rel <= tol
+    assert np.all(rmse <= 1.25 * noise + 1e-4)
+    scene.close()
