@@ -725,7 +725,10 @@ int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* c
                   ((rp->flags & RT_RENDER_COSINE_SAMPLING) ? DEPTH_COS_FLAG : 0u);
         a.per_sample = rp->width * rp->height;
         a.total_paths = (unsigned long long)a.per_sample * (rp->sample_end - rp->sample_begin);
-        a.n_paths = (uint32_t)std::max(32, std::min(4096, env_int("RT_CTA_PATHS", 3 * CTA_THREADS))) & ~31u;
+        // pool size: 3 paths per thread (92 KB per block, 196 KB carve-out, ~60 KB of L1); the media kernels keep
+        // ~300 B of spills per thread in local memory and do better with 992 paths (164 KB carve-out, ~92 KB of L1)
+        const int dflt_paths = (s->features & F_MEDIA) ? 992 : 3 * CTA_THREADS;
+        a.n_paths = (uint32_t)std::max(32, std::min(4096, env_int("RT_CTA_PATHS", dflt_paths))) & ~31u;
         a.refill_idle = (uint32_t)std::max(1, std::min(32, env_int("RT_CTA_REFILL", 8)));
         a.seed = rp->seed;
         const size_t smem = cta_smem_bytes(a.n_paths);
