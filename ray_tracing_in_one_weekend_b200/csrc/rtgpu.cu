@@ -734,6 +734,8 @@ int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* c
         const size_t smem = cta_smem_bytes(a.n_paths);
         void* fn = cta_kernel_for(s->features, count, nullptr);
         CU_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        if (std::getenv("RT_CTA_CARVEOUT"))  // development: shared-memory carve-out in percent (the rest is L1)
+            CU_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, env_int("RT_CTA_CARVEOUT", 100)));
         int bps = 0;
         CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, fn, CTA_THREADS, smem));
         if (bps < 1) return fail(RT_ERR_CUDA, "CTA wavefront kernel does not fit on an SM");
