@@ -36,6 +36,23 @@ MAX_DEPTH = 50
 KERNEL_NAMES = {1: "k_render_mega", 2: "k_wf_traverse + k_wf_shade (CUDA graph)", 3: "k_render_cta"}
 
 
+SCENE_NOTES = {
+    "sphere_scene": "reference cover scene, 533 spheres, demo_scene.rs:37-86",
+    "textured": "cover-scene generator with checker ground, Perlin and earthmap spheres (BASELINE configs[1])",
+    "cornell_box": "demo_scene.rs:112-148, smoke boxes (BASELINE configs[2])",
+    "cornell_box_solid": "Cornell box with solid rotated boxes (BASELINE configs[2] variant)",
+    "pbr_ibl": "pbr.rs materials under the newport_loft environment map (BASELINE configs[3])",
+    "cover_100k_motion": "cover-scene generator at 99 860 spheres with moving spheres (BASELINE configs[4])",
+    "final_scene": "demo_scene.rs:150-221",
+    "simple_light_scene": "demo_scene.rs:88-110",
+    "test_sphere": "demo_scene.rs:229-244, the scene main() renders",
+}
+
+
+def scene_note(name):
+    return SCENE_NOTES.get(name, "extension scene")
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -155,7 +172,7 @@ def run_reference(args, rank):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total_s / max(1, len(vals)),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "mrays_s": sum(v["rays"] for v in vals) / total_s / 1e6,
-        "config": {"workload": f"{args.scene} (reference cover scene, 533 spheres) {args.width}x{args.height}, depth {MAX_DEPTH}; "
+        "config": {"workload": f"{args.scene} ({scene_note(args.scene)}) {args.width}x{args.height}, depth {MAX_DEPTH}; "
                                "each step = a bounded strided column sample at 16 spp",
                    "scene": args.scene, "width": args.width, "height": args.height, "max_depth": MAX_DEPTH},
         "cpu_baseline": {"value": value, "unit": "Mpaths/s", "cores": last["threads"], "kind": "port",
@@ -335,7 +352,7 @@ def run_ours(args, rank, world, local_rank):
             "warmup": max(3, args.warmup), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "mrays_s": mrays, "rays_per_path": rays_per_step / paths_per_step,
-            "config": {"workload": f"{args.scene} (reference cover scene, 533 spheres) {W}x{H}, {SPP} spp per GPU "
+            "config": {"workload": f"{args.scene} ({scene_note(args.scene)}) {W}x{H}, {SPP} spp per GPU "
                                    f"({spp_total} spp frame), depth {MAX_DEPTH}, spp-partitioned + one NCCL reduce",
                        "scene": args.scene, "width": W, "height": H, "spp_per_gpu": SPP, "spp_total": spp_total,
                        "max_depth": MAX_DEPTH, "mode": int(st.mode_used), "parallelism": f"spp-split x{world}",
