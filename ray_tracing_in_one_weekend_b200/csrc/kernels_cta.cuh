@@ -53,12 +53,15 @@ struct CtaArgs {
     uint32_t per_sample;   // width * height (< 2^31)
     uint32_t n_paths;      // N: paths per block pool (multiple of 32, <= 4096)
     uint32_t refill_idle;  // a warp retires/refills once this many of its lanes are idle
-    uint32_t pad0;
+    uint32_t stage_perlin;  // 1: Perlin table 0 is copied into shared memory (scenes with Diffuse(PerlinTex))
     uint64_t seed;
 };
 
 // Bytes of dynamic shared memory for a pool of n paths.
-inline size_t cta_smem_bytes(uint32_t n) { return (size_t)n * (64 + 2 * (CLS_COUNT + 2)); }
+constexpr size_t CTA_PERLIN_BYTES = 256 * 16 + 768;
+inline size_t cta_smem_bytes(uint32_t n, bool perlin) {
+    return (((size_t)n * (64 + 2 * (CLS_COUNT + 2)) + 15) & ~(size_t)15) + (perlin ? CTA_PERLIN_BYTES : 0);
+}
 
 struct CtaPool {
     float4* o;       // o.xyz, time
@@ -68,6 +71,7 @@ struct CtaPool {
     uint16_t* list;  // [CLS_COUNT][N] path ids per shading class
     uint16_t* dead;  // [N] path ids to regenerate
     uint16_t* todo;  // [N] path ids to traverse next: scattered paths (in shading order), then the regenerated ones
+    const float4* perlin;  // Perlin table 0 (256 gradients, then 768 permutation bytes) or nullptr
     uint32_t N;
 };
 
@@ -103,7 +107,7 @@ RT_DEV void cta_shade_item(const DeviceScene& sc, const CtaArgs& a, const CtaPoo
         HitRec rec = fill_hit<F>(sc, ray, mm.w, __uint_as_float(mm.z), want_uv);
         V3f emitted, att;
         Ray scattered;
-        bool ok = shade_cls<CLS>(sc, m, ray, rec, rng, emitted, att, scattered, (a.max_depth & DEPTH_COS_FLAG) != 0u);
+        bool ok = shade_cls<CLS>(sc, m, ray, rec, rng, emitted, att, scattered, (a.max_depth & DEPTH_COS_FLAG) != 0u, P.perlin);
         if (CLS == CLS_CLASSIC) add = beta * emitted;  // main.rs:47 (only Emission emits, material.rs:26-28)
         if (ok && (a.max_depth & DEPTH_RR_FLAG)) ok = russian_roulette(att, rng);
         if (ok) {                                      // main.rs:48-54
@@ -206,6 +210,13 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
     P.dead = P.list + (size_t)CLS_COUNT * N;
     P.todo = P.dead + N;
     P.N = N;
+    P.perlin = nullptr;
+    if (a.stage_perlin) {
+        float4* dst = reinterpret_cast<float4*>(reinterpret_cast<char*>(cta_smem) + (((size_t)N * (64 + 2 * (CLS_COUNT + 2)) + 15) & ~(size_t)15));
+        for (uint32_t i = tid; i < 256u + 48u; i += CTA_THREADS)  // 256 gradients + 768 permutation bytes as 48 float4
+            dst[i] = i < 256u ? __ldg(sc.perlin_grad_lin + i) : __ldg(reinterpret_cast<const float4*>(sc.perlin_perm) + (i - 256u));
+        P.perlin = dst;
+    }
 
     for (uint32_t i = tid; i < N; i += CTA_THREADS) {
         P.d[i] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(0u));

@@ -400,6 +400,8 @@ int rt_scene_create_ex(const RtFlatScene* desc, int device, uint32_t flags, RtSc
         CU_TRY(cudaCreateTextureObject(&to, &rd, &td, nullptr));
         s->texobjs.push_back(to);
         s->ds.perlin_grad = to;
+        s->ds.perlin_grad_lin = dgrad;
+        s->ds.n_perlin = desc->n_perlin;
     }
     // images: uchar4 CUDA arrays behind point-sampled, clamped, unnormalised texture objects
     {
@@ -725,13 +727,17 @@ int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* c
                   ((rp->flags & RT_RENDER_COSINE_SAMPLING) ? DEPTH_COS_FLAG : 0u);
         a.per_sample = rp->width * rp->height;
         a.total_paths = (unsigned long long)a.per_sample * (rp->sample_end - rp->sample_begin);
-        // pool size: 3 paths per thread (92 KB per block, 196 KB carve-out, ~60 KB of L1); the media kernels keep
-        // ~300 B of spills per thread in local memory and do better with 992 paths (164 KB carve-out, ~92 KB of L1)
-        const int dflt_paths = (s->features & F_MEDIA) ? 992 : 3 * CTA_THREADS;
+        // Pool size: 3 paths per thread (92 KB per block, 196 KB carve-out, ~60 KB of L1); the media kernels keep
+        // ~300 B of spills per thread in local memory and do better with 992 paths (164 KB carve-out, ~92 KB of L1).
+        // Scenes with Diffuse(PerlinTex) (and no media) stage Perlin table 0 in shared memory (4.75 KB): one warp's
+        // worth of paths less keeps the block inside the same carve-out (+2..8 % on those scenes).
+        const bool media = (s->features & F_MEDIA) != 0;
+        a.stage_perlin = !media && (s->class_mask >> CLS_DIFFUSE_PERLIN & 1u) && s->ds.n_perlin > 0 ? 1u : 0u;
+        const int dflt_paths = media ? 992 : (a.stage_perlin ? 1120 : 3 * CTA_THREADS);
         a.n_paths = (uint32_t)std::max(32, std::min(4096, env_int("RT_CTA_PATHS", dflt_paths))) & ~31u;
         a.refill_idle = (uint32_t)std::max(1, std::min(32, env_int("RT_CTA_REFILL", 8)));
         a.seed = rp->seed;
-        const size_t smem = cta_smem_bytes(a.n_paths);
+        const size_t smem = cta_smem_bytes(a.n_paths, a.stage_perlin != 0u);
         void* fn = cta_kernel_for(s->features, count, nullptr);
         CU_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         if (std::getenv("RT_CTA_CARVEOUT"))  // development: shared-memory carve-out in percent (the rest is L1)
