@@ -341,7 +341,7 @@ def run_ours(args, rank, world, local_rank):
         # workload differs from the captured one)
         traffic = None
         try:
-            tj = json.load(open(os.path.join(REPO, "profiles", "r01_cta_v4_traffic.json")))
+            tj = json.load(open(os.path.join(REPO, "profiles", "r01_cta_traffic.json")))
             m = tj["match"]
             if (m["scene"], m["width"], m["height"], m["spp_per_gpu"], m["mode"]) == (args.scene, W, H, SPP, int(st.mode_used)):
                 traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
