@@ -34,7 +34,7 @@ typedef enum RtStatus {
     RT_OK = 0,
     RT_ERR_ARG = -1,      /* bad argument / inconsistent scene description */
     RT_ERR_CUDA = -2,     /* CUDA runtime error (no device, OOM, launch failure) */
-    RT_ERR_IO = -3,       /* asset file missing/unreadable (host scene builders only) */
+    RT_ERR_IO = -3,       /* asset file missing/unreadable (host scene builders), PNG file not writable */
     RT_ERR_UNSUPPORTED = -4
 } RtStatus;
 
@@ -253,7 +253,7 @@ int rt_closest_hit_device(RtScene* scene, const float* o_xyz, const float* d_xyz
 int rt_camera_get_rays(const RtCamera* cam, const float* uv, size_t n, float* o_xyz, float* d_xyz);
 
 typedef enum RtRenderMode {
-    RT_MODE_AUTO = 0,
+    RT_MODE_AUTO = 0,       /* = RT_MODE_CTA_WAVEFRONT, the fastest on every measured scene */
     RT_MODE_MEGAKERNEL = 1, /* persistent per-thread path loop with in-warp path regeneration */
     RT_MODE_WAVEFRONT = 2,  /* raygen / traverse / shade+compact kernels over ray queues in device memory */
     RT_MODE_CTA_WAVEFRONT = 3 /* one persistent kernel; every thread block runs the wavefront loop on a
