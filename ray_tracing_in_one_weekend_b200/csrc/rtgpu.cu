@@ -177,7 +177,8 @@ uint32_t material_class(const RtFlatScene* d, const RtMaterial& m) {
     return (uint32_t)CLS_CLASSIC;
 }
 
-DevPrim make_dev_prim(const RtFlatScene* d, uint32_t flat, std::vector<DevMotion>& motion, const std::vector<uint32_t>& flat_to_dev) {
+DevPrim make_dev_prim(const RtFlatScene* d, uint32_t flat, uint32_t dev_index, std::vector<DevMotion>& motion,
+                      const std::vector<uint32_t>& flat_to_dev) {
     const RtPrim& p = d->prims[flat];
     DevPrim q{};
     q.mat = p.mat;
@@ -196,8 +197,11 @@ DevPrim make_dev_prim(const RtFlatScene* d, uint32_t flat, std::vector<DevMotion
             m.dcx = p.g[4] - p.g[0]; m.dcy = p.g[5] - p.g[1]; m.dcz = p.g[6] - p.g[2];
             m.time0 = p.g[7];
             m.dt = p.g[8] - p.g[7];
-            q.x = (uint32_t)motion.size();
-            motion.push_back(m);
+            // the motion table runs parallel to the device primitive array (rt_device.cuh load_motion): the
+            // kernels load record dev_index together with the primitive, q.x is informational
+            if (motion.size() <= dev_index) motion.resize((size_t)dev_index + 1, DevMotion{0.0f, 0.0f, 0.0f, 0.0f, 1.0f, 0.0f, 0.0f, 0.0f});
+            motion[dev_index] = m;
+            q.x = dev_index;
             break;
         }
         case RT_PRIM_XYRECT:  // plane z; a = x, b = y
@@ -322,9 +326,12 @@ int rt_scene_create_ex(const RtFlatScene* desc, int device, uint32_t flags, RtSc
     std::vector<DevPrim> prims(order.size());
     bool has_media = false;
     for (uint32_t k = 0; k < order.size(); k++) {
-        prims[k] = make_dev_prim(desc, order[k], motion, flat_to_dev);
+        prims[k] = make_dev_prim(desc, order[k], k, motion, flat_to_dev);
         has_media |= desc->prims[order[k]].kind == RT_PRIM_MEDIUM;
     }
+    // one record per primitive (static ones: dc = 0, dt = 1): every kernel built with F_MOTION loads record i with
+    // primitive i, and the megakernel / wavefront / batch entry points run the all-features build on any scene
+    motion.resize(order.size(), DevMotion{0.0f, 0.0f, 0.0f, 0.0f, 1.0f, 0.0f, 0.0f, 0.0f});
     // boundary ranges must stay contiguous on the device
     for (uint32_t i = 0; i < desc->n_prims; i++)
         if (desc->prims[i].kind == RT_PRIM_MEDIUM)
