@@ -12,7 +12,8 @@
 #define RT_CAT(a, b) RT_CAT2(a, b)
 
 namespace rtb {
-void* RT_CAT(cta_kernel_f, RT_CTA_F)(bool count) {
+void* RT_CAT(cta_kernel_f, RT_CTA_F)(bool count, int* threads) {
+    if (threads) *threads = CTA_THREADS;
     return count ? (void*)k_render_cta<(uint32_t)RT_CTA_F, true> : (void*)k_render_cta<(uint32_t)RT_CTA_F, false>;
 }
 }  // namespace rtb

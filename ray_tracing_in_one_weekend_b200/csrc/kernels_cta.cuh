@@ -1,6 +1,6 @@
 // CTA-local wavefront renderer (sm_100a): the whole wavefront loop runs INSIDE one persistent kernel.
 //
-// Every thread block (384 threads, two blocks per SM) owns a pool of N = 1152 paths in shared memory (64 B of
+// Every thread block (384 threads — 320 for the media feature sets — two blocks per SM) owns a pool of N = 1152 paths in shared memory (64 B of
 // path state + 18 B of queue space per path = 92 KB per block out of Blackwell's 227 KB per SM) and iterates,
 // separated by __syncthreads():
 //
@@ -30,8 +30,16 @@
 
 namespace rtb {
 
+// Block size per feature set (every translation unit exports its own through cta_kernel_f<F>): the media sets
+// need ~100 registers per thread; at 384 threads x 2 blocks (80 registers) they carry 320-370 B of spills, at 320
+// threads (96 registers, 20 warps per SM) 56 B — final_scene +15 %, cornell_box +7 % (B200, 1080p).  Every other
+// set fits 80 registers and prefers the four extra warps (cornell_box_solid, cover_100k_motion: -1..-4 % at 320/352).
 #ifndef RT_CTA_THREADS
+#if defined(RT_CTA_F) && ((RT_CTA_F) & 2)
+#define RT_CTA_THREADS 320
+#else
 #define RT_CTA_THREADS 384
+#endif
 #endif
 #ifndef RT_CTA_MIN_BLOCKS
 #define RT_CTA_MIN_BLOCKS 2  // register cap 85 (80 used): fits traversal and the common shading classes
@@ -450,25 +458,25 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
 
 // Host-side entry points, one translation unit per instantiated feature set (cta_inst.cu, -DRT_CTA_F=<F>).
 // Feature sets built: 0 (spheres only), F_MOTION, F_RECT, F_RECT|F_XFORM, F_RECT|F_XFORM|F_MEDIA, F_ALL.
-void* cta_kernel_f0(bool count);
-void* cta_kernel_f4(bool count);
-void* cta_kernel_f8(bool count);
-void* cta_kernel_f9(bool count);
-void* cta_kernel_f11(bool count);
-void* cta_kernel_f15(bool count);
+void* cta_kernel_f0(bool count, int* threads);  // *threads = block size the kernel was built for
+void* cta_kernel_f4(bool count, int* threads);
+void* cta_kernel_f8(bool count, int* threads);
+void* cta_kernel_f9(bool count, int* threads);
+void* cta_kernel_f11(bool count, int* threads);
+void* cta_kernel_f15(bool count, int* threads);
 
 // The kernel of the smallest built feature set that covers `features`.
-inline void* cta_kernel_for(uint32_t features, bool count, uint32_t* built) {
-    struct E { uint32_t f; void* (*fn)(bool); };
+inline void* cta_kernel_for(uint32_t features, bool count, uint32_t* built, int* threads) {
+    struct E { uint32_t f; void* (*fn)(bool, int*); };
     const E table[] = {{0u, cta_kernel_f0}, {4u, cta_kernel_f4}, {8u, cta_kernel_f8}, {9u, cta_kernel_f9},
                        {11u, cta_kernel_f11}, {15u, cta_kernel_f15}};
     for (const E& e : table)
         if ((features & ~e.f) == 0u) {
             if (built) *built = e.f;
-            return e.fn(count);
+            return e.fn(count, threads);
         }
     if (built) *built = 15u;
-    return cta_kernel_f15(count);
+    return cta_kernel_f15(count, threads);
 }
 
 }  // namespace rtb

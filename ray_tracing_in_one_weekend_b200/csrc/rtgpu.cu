@@ -734,23 +734,24 @@ int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* c
                   ((rp->flags & RT_RENDER_COSINE_SAMPLING) ? DEPTH_COS_FLAG : 0u);
         a.per_sample = rp->width * rp->height;
         a.total_paths = (unsigned long long)a.per_sample * (rp->sample_end - rp->sample_begin);
-        // Pool size: 3 paths per thread (92 KB per block, 196 KB carve-out, ~60 KB of L1); the media kernels keep
-        // ~300 B of spills per thread in local memory and do better with 992 paths (164 KB carve-out, ~92 KB of L1).
+        // Pool size: 1152 paths (92 KB per block, 196 KB carve-out, ~60 KB of L1) = 3 paths per thread of a 384-thread
+        // block, 3.6 per thread of the 320-thread blocks of the media kernels (measured: 1152 > 1120 > 992 > 864).
         // Scenes with Diffuse(PerlinTex) (and no media) stage Perlin table 0 in shared memory (4.75 KB): one warp's
         // worth of paths less keeps the block inside the same carve-out (+2..8 % on those scenes).
         const bool media = (s->features & F_MEDIA) != 0;
         a.stage_perlin = !media && (s->class_mask >> CLS_DIFFUSE_PERLIN & 1u) && s->ds.n_perlin > 0 ? 1u : 0u;
-        const int dflt_paths = media ? 992 : (a.stage_perlin ? 1120 : 3 * CTA_THREADS);
+        int threads = 0;
+        void* fn = cta_kernel_for(s->features, count, nullptr, &threads);
+        const int dflt_paths = a.stage_perlin ? 1120 : 1152;
         a.n_paths = (uint32_t)std::max(32, std::min(4096, env_int("RT_CTA_PATHS", dflt_paths))) & ~31u;
         a.refill_idle = (uint32_t)std::max(1, std::min(32, env_int("RT_CTA_REFILL", 8)));
         a.seed = rp->seed;
         const size_t smem = cta_smem_bytes(a.n_paths, a.stage_perlin != 0u);
-        void* fn = cta_kernel_for(s->features, count, nullptr);
         CU_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         if (std::getenv("RT_CTA_CARVEOUT"))  // development: shared-memory carve-out in percent (the rest is L1)
             CU_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, env_int("RT_CTA_CARVEOUT", 100)));
         int bps = 0;
-        CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, fn, CTA_THREADS, smem));
+        CU_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, fn, threads, smem));
         if (bps < 1) return fail(RT_ERR_CUDA, "CTA wavefront kernel does not fit on an SM");
         bps = std::min(bps, env_int("RT_CTA_BLOCKS", 64));
         // never more blocks than there are pools of work
@@ -758,7 +759,7 @@ int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* c
         const unsigned grid = (unsigned)std::max<unsigned long long>(1, std::min<unsigned long long>(want, (unsigned long long)s->sm_count * bps));
         CU_TRY(cudaEventRecord(s->ev0, st));
         void* args[2] = {(void*)&s->ds, (void*)&a};
-        CU_TRY(cudaLaunchKernel(fn, dim3(grid), dim3(CTA_THREADS), args, smem, st));
+        CU_TRY(cudaLaunchKernel(fn, dim3(grid), dim3((unsigned)threads), args, smem, st));
         CU_TRY(cudaEventRecord(s->ev1, st));
         if (stats) {
             std::memset(stats, 0, sizeof(*stats));
