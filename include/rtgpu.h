@@ -225,6 +225,15 @@ typedef struct RtBvhInfo {
 } RtBvhInfo;
 int rt_scene_bvh_info(const RtScene* scene, RtBvhInfo* out);
 
+/* Host-only planning step of rt_scene_create, exposed for inspection and tests (no device needed): how the
+ * CTA-wavefront renderer's shade queues are assigned for this scene.  The renderer sorts the hits of an iteration
+ * into 7 queues per block before shading them (the "material-sorted shade pass"): queue 0 takes the misses
+ * (main.rs:58), every shading class of the scene gets one, and the queues the scene leaves free go to its heaviest
+ * (material kind, texture kind) groups, so that a warp shades ONE kind of material (src/material.rs, src/pbr.rs)
+ * wherever the scene allows it.  mat_queue[n_materials]: queue of every material; *q_class / *q_order: 4 bits per
+ * queue — the shading class queue q runs, and the order the queues are drained in (most expensive first). */
+int rt_flat_shade_queues(const RtFlatScene* desc, uint8_t* mat_queue, uint32_t* q_class, uint32_t* q_order);
+
 /* Result of one closest-hit query == the fields of the reference's HitRecord that a primitive
  * writes (src/hitable.rs:13-22).  prim = -1 on a miss (then the other fields are 0). */
 typedef struct RtHit {

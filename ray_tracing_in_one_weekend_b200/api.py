@@ -128,7 +128,7 @@ class RtStats(C.Structure):
 EXPORTED_SYMBOLS = [
     "rt_scene_create", "rt_scene_create_ex", "rt_scene_destroy", "rt_scene_bvh_info", "rt_closest_hit", "rt_closest_hit_device",
     "rt_camera_get_rays", "rt_render_device", "rt_render", "rt_resolve_rgb8", "rt_write_png", "rt_measure_fp32_peak",
-    "rt_last_error", "rt_host_scene_build", "rt_host_scene_flat", "rt_host_scene_destroy",
+    "rt_flat_shade_queues", "rt_last_error", "rt_host_scene_build", "rt_host_scene_flat", "rt_host_scene_destroy",
 ]
 
 _lib: Optional[C.CDLL] = None
@@ -150,6 +150,7 @@ def load_library() -> C.CDLL:
     lib.rt_scene_destroy.argtypes = [vp]
     lib.rt_scene_destroy.restype = None
     lib.rt_scene_bvh_info.argtypes = [vp, C.POINTER(RtBvhInfo)]
+    lib.rt_flat_shade_queues.argtypes = [vp, C.POINTER(C.c_uint8), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
     lib.rt_closest_hit.argtypes = [vp, vp, vp, vp, sz, C.c_float, C.c_float, vp]
     lib.rt_closest_hit_device.argtypes = [vp, vp, vp, vp, sz, C.c_float, C.c_float, vp, vp]
     lib.rt_camera_get_rays.argtypes = [C.POINTER(RtCamera), vp, sz, vp, vp]
@@ -198,6 +199,16 @@ class HostScene:
     @property
     def flat(self) -> "C.POINTER(RtFlatScene)":
         return self._lib.rt_host_scene_flat(self._h)
+
+    def shade_queues(self):
+        """(queue of every material, class of every queue, drain order): the host-side planning step of the
+        CTA-wavefront renderer's material-sorted shade pass (rt_flat_shade_queues; no device needed)."""
+        flat = self.flat
+        n = flat.contents.n_materials
+        mq = (C.c_uint8 * max(n, 1))()
+        qc, qo = C.c_uint32(), C.c_uint32()
+        _check(self._lib.rt_flat_shade_queues(flat, mq, C.byref(qc), C.byref(qo)))
+        return (list(mq)[:n], [(qc.value >> (4 * q)) & 15 for q in range(7)], [(qo.value >> (4 * q)) & 15 for q in range(7)])
 
     def close(self) -> None:
         if getattr(self, "_h", None):

@@ -28,7 +28,7 @@ constexpr uint32_t LEAF_FIRST_MASK = (1u << 27) - 1;  // 134M primitives
 //                medium: neg_inv_density, bits(first boundary device prim), bits(boundary count), 0
 //   q1.x         rect: b1 (float);  moving sphere: bits(index into DeviceScene::motion)
 //   q1.y         material index
-//   q1.z         kind | flags << 8 | xform chain << 16
+//   q1.z         kind | boundary-only flag << 8 | CTA shade queue << 9 | shading class << 12 | xform chain << 16
 //   q1.w         flat index (position in RtFlatScene.prims == the reference's visitation order)
 struct alignas(32) DevPrim {
     float g0, g1, g2, g3;

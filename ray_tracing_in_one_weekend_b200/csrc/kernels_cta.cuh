@@ -11,10 +11,12 @@
 //                   per lane, while-while BVH traversal (rt_device.cuh); idle lanes are refilled from the
 //                   counter as soon as `refill_idle` lanes of the warp are idle.  A1: then the camera rays, a
 //                   coherent warp of 32 at a time, run to completion (uniform chunks that fill the tail).
-//                   A lane that finishes writes (t, prim) back and appends the path to the shared-memory
-//                   queue of its SHADING CLASS
-//   C  shade        warps pull 32-entry chunks of the class queues from a counter, most expensive class
-//                   first (every class range padded to a warp multiple, so a warp runs ONE material group):
+//                   A lane that finishes writes (t, prim) back and appends the path to one of the block's seven
+//                   SHADE QUEUES in shared memory: queue 0 for a miss, else bits 9..11 of the primitive record.
+//                   The host assigns the queues per scene (rtgpu.cu assign_shade_queues): one per shading class
+//                   in use, the free ones to the heaviest material kinds of the mixed classes (pbr.rs, "classic")
+//   C  shade        warps pull 32-entry chunks of the queues from a counter, most expensive class first
+//                   (every queue range padded to a warp multiple, so a warp runs ONE material group):
 //                   sky / emitted / scatter (material.rs, pbr.rs, texture.rs), radiance to the frame with
 //                   red.global.add.f32, the scattered ray back into the slot and onto the todo list, or the
 //                   slot onto the dead list
@@ -62,6 +64,9 @@ struct CtaArgs {
     uint32_t n_paths;      // N: paths per block pool (multiple of 32, <= 4096)
     uint32_t refill_idle;  // a warp retires/refills once this many of its lanes are idle
     uint32_t stage_perlin;  // 1: Perlin table 0 is copied into shared memory (scenes with Diffuse(PerlinTex))
+    // Shade queues (rtgpu.cu assign_shade_queues): queue 0 = misses, queue q = bits 9..11 of the hit primitive's
+    // record.  4 bits per entry: the shading class (CLS_*) queue q runs, and the order the shade phase drains them in.
+    uint32_t q_cls, q_order;
     uint64_t seed;
 };
 
@@ -190,7 +195,7 @@ RT_DEV void cta_retire(const CtaPool& P, CtaLane& L, uint32_t* s_cnt) {
         uint2* st = reinterpret_cast<uint2*>(P.m + L.pid);
         *st = make_uint2((uint32_t)L.rng.state, (uint32_t)(L.rng.state >> 32));
     }
-    const uint32_t cls = L.ts.best_prim == 0xffffffffu ? (uint32_t)CLS_MISS : ((L.ts.best_kfx >> 12) & 0xfu);
+    const uint32_t cls = L.ts.best_prim == 0xffffffffu ? 0u : ((L.ts.best_kfx >> 9) & 0x7u);  // shade queue
     const uint32_t pos = atomicAdd(&s_cnt[cls], 1u);
     P.list[cls * P.N + pos] = (uint16_t)L.pid;
     L.pid = CTA_NONE;
@@ -379,12 +384,10 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
         {
             // Class ranges in a common index space, each padded to a warp multiple, the most expensive class
             // first; warps pull 32-entry chunks from a counter (longest-processing-time-first keeps the tail short).
-            constexpr int ORDER[CLS_COUNT] = {CLS_DIFFUSE_PERLIN, CLS_PBR, CLS_CLASSIC, CLS_DIELECTRIC,
-                                              CLS_DIFFUSE_CONST, CLS_METAL, CLS_MISS};
             uint32_t start[CLS_COUNT + 1];
             start[0] = 0u;
 #pragma unroll
-            for (int c = 0; c < CLS_COUNT; c++) start[c + 1] = start[c] + ((s_cnt[ORDER[c]] + 31u) & ~31u);
+            for (int c = 0; c < CLS_COUNT; c++) start[c + 1] = start[c] + ((s_cnt[(a.q_order >> (4 * c)) & 0x7u] + 31u) & ~31u);
             for (;;) {
                 uint32_t g = 0;
                 if (lane == 0) g = atomicAdd(&s_chunk, 32u);
@@ -394,15 +397,13 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
 #pragma unroll
                 for (int c = 1; c < CLS_COUNT; c++) k += g >= start[c] ? 1 : 0;
                 uint32_t first = 0;
-                int cls = ORDER[0];
 #pragma unroll
-                for (int c = 1; c < CLS_COUNT; c++) {
-                    first = k == c ? start[c] : first;
-                    cls = k == c ? ORDER[c] : cls;
-                }
+                for (int c = 1; c < CLS_COUNT; c++) first = k == c ? start[c] : first;
+                const uint32_t q = (a.q_order >> (4 * k)) & 0x7u;   // queue of this chunk
+                const int cls = (int)((a.q_cls >> (4 * q)) & 0xfu);  // the class it shades as
                 const uint32_t idx = g - first + lane;
-                if (idx < s_cnt[cls]) {
-                    const uint32_t pid = P.list[(uint32_t)cls * N + idx];
+                if (idx < s_cnt[q]) {
+                    const uint32_t pid = P.list[q * N + idx];
                     switch (cls) {
                         case CLS_MISS: cta_shade_item<F, CLS_MISS>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
                         case CLS_DIFFUSE_CONST: cta_shade_item<F, CLS_DIFFUSE_CONST>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;

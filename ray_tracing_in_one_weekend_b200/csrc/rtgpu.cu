@@ -1,7 +1,9 @@
 // librtgpu.so — C ABI entry points (include/rtgpu.h): scene upload, batch closest hit, render,
 // resolve, FP32 peak probe.  There is no CPU fallback: without a usable CUDA device every compute
 // entry point fails with RT_ERR_CUDA.
+#include <algorithm>
 #include <chrono>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -54,6 +56,8 @@ struct RtScene {
     int mega_blocks_per_sm = 0, mega_blocks_per_sm_cnt = 0, sm_count = 0;
     uint32_t features = 0;  // F_* bits present in the scene
     uint32_t class_mask = 0;  // shading classes (CLS_*) of the scene's materials
+    // CTA wavefront: shade queue -> class (4 bits per queue) and the order the shade phase drains the queues in
+    uint32_t q_cls = 0, q_order = 0;
     // wavefront pool + the CUDA graph of WF_GRAPH_ITERS iterations (built on first use)
     WfArgs wf[WF_MAX_CHAINS]{};  // independent sub-pools ("chains") whose kernels overlap on the GPU
     int wf_chains = 0;
@@ -177,13 +181,109 @@ uint32_t material_class(const RtFlatScene* d, const RtMaterial& m) {
     return (uint32_t)CLS_CLASSIC;
 }
 
+// Shade queues of the CTA wavefront renderer.  The kernel has CLS_COUNT queues per block: queue 0 takes the misses
+// and every shading class of the scene needs one; the queues a scene leaves free are handed to the heaviest
+// (material kind, texture kind) groups of its multi-kind classes (CLS_PBR, CLS_CLASSIC), so that a warp of the shade
+// phase runs ONE material kind wherever the scene allows it (pbr_ibl: seven pbr.rs kinds in one class otherwise).
+// Weight of a group = surface area of the world primitives that carry it (a proxy for how often it is hit).
+struct ShadeQueues {
+    std::vector<uint8_t> mat_queue;  // per material
+    uint32_t q_cls = 0, q_order = 0;
+};
+int env_int(const char* name, int dflt);
+ShadeQueues assign_shade_queues(const RtFlatScene* d) {
+    ShadeQueues out;
+    out.mat_queue.assign(d->n_materials, 0);
+    auto sig_of = [&](const RtMaterial& m) {
+        const bool t0 = !(m.kind == RT_MAT_METAL || m.kind == RT_MAT_DIELECTRIC || m.kind == RT_MAT_DISNEY_CLEARCOAT);
+        return material_class(d, m) | (m.kind << 8) | ((t0 ? d->textures[m.tex0].kind + 1u : 0u) << 16);
+    };
+    std::vector<double> mat_w(d->n_materials, 0.0);
+    std::vector<char> used(d->n_materials, 0);
+    for (uint32_t i = 0; i < d->n_prims; i++) {
+        const RtPrim& p = d->prims[i];
+        if (p.mat >= d->n_materials) continue;
+        double w = 1.0;
+        if (p.kind == RT_PRIM_SPHERE || p.kind == RT_PRIM_MOVING_SPHERE) {
+            w = 12.566370614359172 * (double)p.g[3] * (double)p.g[3];
+        } else if (p.kind == RT_PRIM_XYRECT || p.kind == RT_PRIM_XZRECT || p.kind == RT_PRIM_YZRECT) {
+            w = 1.0;
+            for (int k = 0; k < 3; k++) {
+                const double e = std::fabs((double)p.g[3 + k] - (double)p.g[k]);
+                if (e > 0.0) w *= e;
+            }
+        }
+        mat_w[p.mat] += w;
+        used[p.mat] = 1;
+    }
+    struct Group { uint32_t sig; double w; int queue; };
+    std::vector<Group> groups;
+    for (uint32_t i = 0; i < d->n_materials; i++) {
+        if (!used[i]) continue;
+        const uint32_t sg = sig_of(d->materials[i]);
+        auto it = std::find_if(groups.begin(), groups.end(), [&](const Group& g) { return g.sig == sg; });
+        if (it == groups.end()) groups.push_back(Group{sg, mat_w[i], -1});
+        else it->w += mat_w[i];
+    }
+    // one queue per class in use ...
+    int cls_queue[CLS_COUNT];
+    uint8_t q_cls[8] = {(uint8_t)CLS_MISS, 0, 0, 0, 0, 0, 0, 0};
+    int n_q = 1;
+    for (int c = 1; c < CLS_COUNT; c++) {
+        cls_queue[c] = -1;
+        if (std::any_of(groups.begin(), groups.end(), [&](const Group& g) { return (int)(g.sig & 0xffu) == c; })) {
+            cls_queue[c] = n_q;
+            q_cls[n_q++] = (uint8_t)c;
+        }
+    }
+    // ... and the free ones to the heaviest group of a class whose queue still mixes several groups
+    const bool split = env_int("RT_CTA_SPLIT_QUEUES", 1) != 0;  // development knob: 0 = one queue per class
+    for (; split && n_q < CLS_COUNT; n_q++) {
+        Group* best = nullptr;
+        for (Group& g : groups) {
+            if (g.queue >= 0) continue;
+            const uint32_t c = g.sig & 0xffu;
+            const auto shared = std::count_if(groups.begin(), groups.end(), [&](const Group& h) { return (h.sig & 0xffu) == c && h.queue < 0; });
+            if (shared >= 2 && (!best || g.w > best->w)) best = &g;
+        }
+        if (!best) break;
+        best->queue = n_q;
+        q_cls[n_q] = (uint8_t)(best->sig & 0xffu);
+    }
+    for (Group& g : groups)
+        if (g.queue < 0) g.queue = cls_queue[g.sig & 0xffu];
+    for (uint32_t i = 0; i < d->n_materials; i++) {
+        if (!used[i]) {  // unreferenced material: any queue of its class (or the class's would-be queue 0 slot)
+            const int c = (int)material_class(d, d->materials[i]);
+            out.mat_queue[i] = (uint8_t)(cls_queue[c] >= 0 ? cls_queue[c] : 0);
+            continue;
+        }
+        const uint32_t sg = sig_of(d->materials[i]);
+        out.mat_queue[i] = (uint8_t)std::find_if(groups.begin(), groups.end(), [&](const Group& g) { return g.sig == sg; })->queue;
+    }
+    // drain order of the shade phase: most expensive class first (long chunks start first), the misses last
+    static const int rank[CLS_COUNT] = {/*MISS*/ 6, /*DIFFUSE_CONST*/ 4, /*METAL*/ 5, /*DIELECTRIC*/ 3, /*PERLIN*/ 0, /*CLASSIC*/ 2, /*PBR*/ 1};
+    int order[CLS_COUNT];
+    for (int q = 0; q < CLS_COUNT; q++) order[q] = q;
+    std::stable_sort(order, order + CLS_COUNT, [&](int a, int b) {
+        const int ra = a < n_q ? rank[q_cls[a]] : 7, rb = b < n_q ? rank[q_cls[b]] : 7;
+        return ra < rb;
+    });
+    for (int q = 0; q < CLS_COUNT; q++) {
+        out.q_cls |= (uint32_t)q_cls[q] << (4 * q);
+        out.q_order |= (uint32_t)order[q] << (4 * q);
+    }
+    return out;
+}
+
 DevPrim make_dev_prim(const RtFlatScene* d, uint32_t flat, uint32_t dev_index, std::vector<DevMotion>& motion,
-                      const std::vector<uint32_t>& flat_to_dev) {
+                      const std::vector<uint32_t>& flat_to_dev, const std::vector<uint8_t>& mat_queue) {
     const RtPrim& p = d->prims[flat];
     DevPrim q{};
     q.mat = p.mat;
-    // kind | flags (4 bits) << 8 | shading class << 12 | transform chain << 16
-    q.kfx = (p.kind & 0xffu) | ((p.flags & 0xfu) << 8) | (material_class(d, d->materials[p.mat]) << 12) | (p.xform << 16);
+    // kind | flag (1 bit) << 8 | CTA shade queue (3 bits) << 9 | shading class << 12 | transform chain << 16
+    q.kfx = (p.kind & 0xffu) | ((p.flags & 0x1u) << 8) | (((uint32_t)mat_queue[p.mat] & 7u) << 9) |
+            (material_class(d, d->materials[p.mat]) << 12) | (p.xform << 16);
     q.flat = flat;
     auto bits = [](uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; };
     auto ubits = [](float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; };
@@ -324,9 +424,13 @@ int rt_scene_create_ex(const RtFlatScene* desc, int device, uint32_t flags, RtSc
     for (uint32_t k = 0; k < order.size(); k++) flat_to_dev[order[k]] = k;
     std::vector<DevMotion> motion;
     std::vector<DevPrim> prims(order.size());
+    const ShadeQueues queues = assign_shade_queues(desc);
+    s->q_cls = queues.q_cls;
+    s->q_order = queues.q_order;
+    if (std::getenv("RT_TIMING")) std::fprintf(stderr, "[rtgpu] shade queues: class per queue %07x, drain order %07x\n", s->q_cls, s->q_order);
     bool has_media = false;
     for (uint32_t k = 0; k < order.size(); k++) {
-        prims[k] = make_dev_prim(desc, order[k], k, motion, flat_to_dev);
+        prims[k] = make_dev_prim(desc, order[k], k, motion, flat_to_dev, queues.mat_queue);
         has_media |= desc->prims[order[k]].kind == RT_PRIM_MEDIUM;
     }
     // one record per primitive (static ones: dc = 0, dt = 1): every kernel built with F_MOTION loads record i with
@@ -482,6 +586,17 @@ int rt_scene_create_ex(const RtFlatScene* desc, int device, uint32_t flags, RtSc
 }
 
 void rt_scene_destroy(RtScene* scene) { delete scene; }
+
+int rt_flat_shade_queues(const RtFlatScene* desc, uint8_t* mat_queue, uint32_t* q_class, uint32_t* q_order) {
+    if (!desc || !mat_queue || !q_class || !q_order) return fail(RT_ERR_ARG, "NULL argument");
+    for (uint32_t i = 0; i < desc->n_prims; i++)
+        if (desc->prims[i].mat >= desc->n_materials) return fail(RT_ERR_ARG, "primitive with a bad material index");
+    const ShadeQueues q = assign_shade_queues(desc);
+    std::memcpy(mat_queue, q.mat_queue.data(), q.mat_queue.size());
+    *q_class = q.q_cls;
+    *q_order = q.q_order;
+    return RT_OK;
+}
 
 int rt_scene_bvh_info(const RtScene* scene, RtBvhInfo* out) {
     if (!scene || !out) return fail(RT_ERR_ARG, "NULL argument");
@@ -746,6 +861,8 @@ int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* c
         a.n_paths = (uint32_t)std::max(32, std::min(4096, env_int("RT_CTA_PATHS", dflt_paths))) & ~31u;
         a.refill_idle = (uint32_t)std::max(1, std::min(32, env_int("RT_CTA_REFILL", 8)));
         a.seed = rp->seed;
+        a.q_cls = s->q_cls;
+        a.q_order = s->q_order;
         const size_t smem = cta_smem_bytes(a.n_paths, a.stage_perlin != 0u);
         CU_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         if (std::getenv("RT_CTA_CARVEOUT"))  // development: shared-memory carve-out in percent (the rest is L1)
@@ -777,7 +894,11 @@ int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* c
             stats->prim_tests = h[4];
             stats->launches = 1;
             stats->mode_used = RT_MODE_CTA_WAVEFRONT;
-            for (int c = 0; c < 8; c++) stats->class_counts[c] = h[8 + c];
+#if RT_CTA_PROFILE
+            for (int c = 0; c < 8; c++) stats->class_counts[c] = h[8 + c];  // development build: phase cycle counters
+#else
+            for (int q = 0; q < CLS_COUNT; q++) stats->class_counts[(s->q_cls >> (4 * q)) & 0xfu] += h[8 + q];  // queue -> class
+#endif
             stats->ms_total = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - w0).count();
         }
         return RT_OK;

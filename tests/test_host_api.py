@@ -134,3 +134,57 @@ def test_png_writer_round_trip(rtlib, tmp_path):
     lib = rtlib.load_library()
     assert lib.rt_write_png(b"/nonexistent_dir/x.png", a.ctypes.data_as(C.c_void_p), 53, 37) == -3
     assert lib.rt_write_png(None, None, 0, 0) == -3
+
+
+def _material_class(m, texs):
+    """rt_device.cuh CLS_*: 1 Diffuse(Constant) 2 Metal 3 Dielectric 4 Diffuse(Perlin) 5 other material.rs 6 pbr.rs."""
+    if m.kind >= 6: return 6
+    if m.kind == 3: return 2
+    if m.kind == 4: return 3
+    if m.kind == 1 and texs[m.tex0].kind == 0: return 1
+    if m.kind == 1 and texs[m.tex0].kind == 2: return 4
+    return 5
+
+
+@pytest.mark.parametrize("name", SCENES)
+def test_shade_queue_assignment(rtlib, name):
+    """rt_flat_shade_queues (the planning step of the material-sorted shade pass): queue 0 is kept for the misses,
+    a queue runs exactly one shading class, materials of the same (class, kind, texture kind) share a queue, free
+    queues are used to separate the kinds of a mixed class, and the drain order is a permutation with the misses
+    after every queue in use."""
+    hs = rtlib.HostScene(name, 1.5)
+    f = hs.flat.contents
+    mats = [f.materials[i] for i in range(f.n_materials)]
+    texs = [f.textures[i] for i in range(f.n_textures)]
+    used = sorted({f.prims[i].mat for i in range(f.n_prims)})
+    mq, q_cls, q_order = hs.shade_queues()
+    assert sorted(q_order) == list(range(7))
+    assert q_cls[0] == 0
+    sig_queue = {}
+    for i in used:
+        m = mats[i]
+        cls = _material_class(m, texs)
+        assert 1 <= mq[i] <= 6 and q_cls[mq[i]] == cls, (i, mq[i], q_cls, cls)
+        has_tex = m.kind not in (3, 4, 12)
+        sig = (cls, m.kind, texs[m.tex0].kind if has_tex else -1)
+        assert sig_queue.setdefault(sig, mq[i]) == mq[i]
+    n_sig, n_queues = len(sig_queue), len(set(sig_queue.values()))
+    assert n_queues == min(n_sig, 6), (sig_queue, q_cls)  # every free queue is used while kinds still share one
+    in_use = set(sig_queue.values())
+    pos = {q: k for k, q in enumerate(q_order)}
+    assert all(pos[q] < pos[0] for q in in_use)           # the misses are drained after every hit queue in use
+    hs.close()
+
+
+def test_shade_queues_split_the_pbr_class(rtlib):
+    """pbr_ibl holds seven pbr.rs material kinds (one class): they are spread over the six hit queues, the ground's
+    RoughPlastic (by far the largest surface) in a queue of its own."""
+    hs = rtlib.HostScene("pbr_ibl", 1.5)
+    f = hs.flat.contents
+    mq, q_cls, _ = hs.shade_queues()
+    assert q_cls[1:7] == [6] * 6
+    ground = max(range(f.n_prims), key=lambda i: f.prims[i].g[3])
+    gq = mq[f.prims[ground].mat]
+    kinds_in_gq = {f.materials[i].kind for i in range(f.n_materials) if mq[i] == gq}
+    assert kinds_in_gq == {8}
+    hs.close()
