@@ -231,7 +231,8 @@ int rt_scene_bvh_info(const RtScene* scene, RtBvhInfo* out);
  * (main.rs:58), every shading class of the scene gets one, and the queues the scene leaves free go to its heaviest
  * (material kind, texture kind) groups, so that a warp shades ONE kind of material (src/material.rs, src/pbr.rs)
  * wherever the scene allows it.  mat_queue[n_materials]: queue of every material; *q_class / *q_order: 4 bits per
- * queue — the shading class queue q runs, and the order the queues are drained in (most expensive first). */
+ * queue — the shading class queue q runs, and the order the queues are drained in (hit queues are numbered most
+ * expensive class first, so this is always 1, 2, ..., 6, 0). */
 int rt_flat_shade_queues(const RtFlatScene* desc, uint8_t* mat_queue, uint32_t* q_class, uint32_t* q_order);
 
 /* Result of one closest-hit query == the fields of the reference's HitRecord that a primitive

@@ -65,8 +65,8 @@ struct CtaArgs {
     uint32_t refill_idle;  // a warp retires/refills once this many of its lanes are idle
     uint32_t stage_perlin;  // 1: Perlin table 0 is copied into shared memory (scenes with Diffuse(PerlinTex))
     // Shade queues (rtgpu.cu assign_shade_queues): queue 0 = misses, queue q = bits 9..11 of the hit primitive's
-    // record.  4 bits per entry: the shading class (CLS_*) queue q runs, and the order the shade phase drains them in.
-    uint32_t q_cls, q_order;
+    // record, numbered most expensive class first.  4 bits per queue: the shading class (CLS_*) it runs.
+    uint32_t q_cls;
     uint64_t seed;
 };
 
@@ -387,7 +387,7 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
             uint32_t start[CLS_COUNT + 1];
             start[0] = 0u;
 #pragma unroll
-            for (int c = 0; c < CLS_COUNT; c++) start[c + 1] = start[c] + ((s_cnt[(a.q_order >> (4 * c)) & 0x7u] + 31u) & ~31u);
+            for (int c = 0; c < CLS_COUNT; c++) start[c + 1] = start[c] + ((s_cnt[(c + 1) % CLS_COUNT] + 31u) & ~31u);  // 1..6, then 0
             for (;;) {
                 uint32_t g = 0;
                 if (lane == 0) g = atomicAdd(&s_chunk, 32u);
@@ -399,7 +399,7 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
                 uint32_t first = 0;
 #pragma unroll
                 for (int c = 1; c < CLS_COUNT; c++) first = k == c ? start[c] : first;
-                const uint32_t q = (a.q_order >> (4 * k)) & 0x7u;   // queue of this chunk
+                const uint32_t q = k == CLS_COUNT - 1 ? 0u : (uint32_t)k + 1u;  // queue of this chunk
                 const int cls = (int)((a.q_cls >> (4 * q)) & 0xfu);  // the class it shades as
                 const uint32_t idx = g - first + lane;
                 if (idx < s_cnt[q]) {

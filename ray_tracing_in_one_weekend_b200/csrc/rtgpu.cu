@@ -261,17 +261,21 @@ ShadeQueues assign_shade_queues(const RtFlatScene* d) {
         const uint32_t sg = sig_of(d->materials[i]);
         out.mat_queue[i] = (uint8_t)std::find_if(groups.begin(), groups.end(), [&](const Group& g) { return g.sig == sg; })->queue;
     }
-    // drain order of the shade phase: most expensive class first (long chunks start first), the misses last
+    // The shade phase drains queues 1, 2, ..., 6 and then 0: renumber the hit queues so that the most expensive
+    // class comes first (its long chunks start first) and the misses last.
     static const int rank[CLS_COUNT] = {/*MISS*/ 6, /*DIFFUSE_CONST*/ 4, /*METAL*/ 5, /*DIELECTRIC*/ 3, /*PERLIN*/ 0, /*CLASSIC*/ 2, /*PBR*/ 1};
-    int order[CLS_COUNT];
-    for (int q = 0; q < CLS_COUNT; q++) order[q] = q;
-    std::stable_sort(order, order + CLS_COUNT, [&](int a, int b) {
-        const int ra = a < n_q ? rank[q_cls[a]] : 7, rb = b < n_q ? rank[q_cls[b]] : 7;
-        return ra < rb;
-    });
+    int by_cost[CLS_COUNT];
+    for (int q = 0; q < CLS_COUNT; q++) by_cost[q] = q;
+    std::stable_sort(by_cost + 1, by_cost + n_q, [&](int a, int b) { return rank[q_cls[a]] < rank[q_cls[b]]; });
+    uint8_t renum[8] = {0, 1, 2, 3, 4, 5, 6, 7}, cls_sorted[8] = {(uint8_t)CLS_MISS, 0, 0, 0, 0, 0, 0, 0};
+    for (int k = 1; k < n_q; k++) {
+        renum[by_cost[k]] = (uint8_t)k;
+        cls_sorted[k] = q_cls[by_cost[k]];
+    }
+    for (auto& mq : out.mat_queue) mq = renum[mq];
     for (int q = 0; q < CLS_COUNT; q++) {
-        out.q_cls |= (uint32_t)q_cls[q] << (4 * q);
-        out.q_order |= (uint32_t)order[q] << (4 * q);
+        out.q_cls |= (uint32_t)cls_sorted[q] << (4 * q);
+        out.q_order |= (uint32_t)((q + 1) % CLS_COUNT) << (4 * q);  // informational: 1, 2, ..., 6, 0
     }
     return out;
 }
@@ -862,7 +866,6 @@ int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* c
         a.refill_idle = (uint32_t)std::max(1, std::min(32, env_int("RT_CTA_REFILL", 8)));
         a.seed = rp->seed;
         a.q_cls = s->q_cls;
-        a.q_order = s->q_order;
         const size_t smem = cta_smem_bytes(a.n_paths, a.stage_perlin != 0u);
         CU_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         if (std::getenv("RT_CTA_CARVEOUT"))  // development: shared-memory carve-out in percent (the rest is L1)

@@ -173,6 +173,9 @@ def test_shade_queue_assignment(rtlib, name):
     in_use = set(sig_queue.values())
     pos = {q: k for k, q in enumerate(q_order)}
     assert all(pos[q] < pos[0] for q in in_use)           # the misses are drained after every hit queue in use
+    rank = {4: 0, 6: 1, 5: 2, 3: 3, 1: 4, 2: 5}            # Perlin, pbr.rs, classic, dielectric, diffuse, metal
+    ranks = [rank[q_cls[q]] for q in sorted(in_use)]
+    assert ranks == sorted(ranks) and sorted(in_use) == list(range(1, len(in_use) + 1))  # numbered by cost, no gaps
     hs.close()
 
 
