@@ -28,6 +28,8 @@ SPP = int(os.environ.get("PARITY_SPP", 4096))
 CASES = [("sphere_scene", 240, 135), ("textured", 240, 135), ("pbr_ibl", 240, 135), ("cover_defocus", 192, 108),
          ("cover_4k_motion", 192, 108), ("cornell_box_solid", 96, 96), ("cornell_box", 80, 80), ("final_scene", 80, 80),
          ("simple_light_scene", 160, 90), ("test_sphere", 200, 100)]
+if os.environ.get("PARITY_CASES"):  # comma-separated subset, e.g. after a change that touches some feature sets only
+    CASES = [c for c in CASES if c[0] in os.environ["PARITY_CASES"].split(",")]
 
 
 def lum(a):
