@@ -5,6 +5,8 @@ The GPU uses its own per-path RNG streams, so the comparison is statistical.  To
     (looser bound 3 sigma-style for the quick low-spp cases);
   * per-channel RMSE(gpu, oracle) <= 1.25 x RMSE(oracle seed A, oracle seed B)  (the noise floor).
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -183,3 +185,39 @@ def test_cosine_sampling_is_unbiased(rtlib, name, tol, mode):
     assert rel <= tol
     assert np.all(rmse <= 1.25 * noise + 1e-4)
     scene.close()
+
+
+@pytest.mark.gpu
+def test_c_example_renders_through_the_c_abi(rtlib, tmp_path):
+    """examples/render_scene.c (C99, only include/rtgpu.h): scene build -> rt_scene_create -> rt_render ->
+    rt_resolve_rgb8 -> rt_write_png, i.e. main.rs:62-129 with the hot path behind the ABI.  The PNG it writes
+    equals the one the ctypes binding produces for the same parameters (same seed, same sample range)."""
+    import subprocess
+    import zlib
+    from test_host_api import _build_c_example
+    repo, exe = _build_c_example(tmp_path)
+    out = tmp_path / "c.png"
+    r = subprocess.run([exe, "test_sphere", "96", "48", "8", os.path.join(repo, "assets"), str(out)],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert f"{96 * 48 * 8} paths" in r.stdout
+    data = out.read_bytes()
+    assert data[:8] == b"\x89PNG\r\n\x1a\n"
+    # decode the single IDAT stream (filter type 0 rows, as rt_write_png emits them)
+    pos, idat = 8, b""
+    while pos < len(data):
+        n = int.from_bytes(data[pos:pos + 4], "big")
+        if data[pos + 4:pos + 8] == b"IDAT":
+            idat += data[pos + 8:pos + 8 + n]
+        pos += 12 + n
+    raw = zlib.decompress(idat)
+    rows = np.frombuffer(raw, np.uint8).reshape(48, 1 + 96 * 3)
+    assert (rows[:, 0] == 0).all()
+    img_c = rows[:, 1:].reshape(48, 96, 3)
+    hs = rtlib.HostScene("test_sphere", 96 / 48)
+    sc = rtlib.Scene(hs.flat, 0)
+    mean, _ = sc.render(96, 48, 8, seed=95)
+    img_py = sc.resolve_rgb8(mean)
+    # radiance is accumulated with float atomics: summation order may flip the last bit before quantisation
+    assert np.abs(img_c.astype(int) - np.asarray(img_py).reshape(48, 96, 3).astype(int)).max() <= 1
+    sc.close()

@@ -191,3 +191,28 @@ def test_shade_queues_split_the_pbr_class(rtlib):
     kinds_in_gq = {f.materials[i].kind for i in range(f.n_materials) if mq[i] == gq}
     assert kinds_in_gq == {8}
     hs.close()
+
+
+def _build_c_example(tmp_path):
+    import subprocess
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    libdir = os.path.join(repo, "ray_tracing_in_one_weekend_b200")
+    exe = str(tmp_path / "render_scene")
+    subprocess.check_call(["gcc", "-std=c99", "-pedantic", "-Wall", "-Wextra", "-Werror", "-I" + os.path.join(repo, "include"),
+                           os.path.join(repo, "examples", "render_scene.c"), "-L" + libdir, "-lrtgpu",
+                           "-Wl,-rpath," + libdir, "-o", exe])
+    return repo, exe
+
+
+def test_header_is_plain_c99_and_the_c_example_links(rtlib, tmp_path):
+    """The boundary is a C ABI: include/rtgpu.h compiles as pedantic C99 and examples/render_scene.c (a C caller
+    with no C++/CUDA/torch on its side) links against librtgpu.so.  Without a GPU it must fail with the library's
+    error code, not abort and not fall back to the CPU."""
+    import subprocess
+    repo, exe = _build_c_example(tmp_path)
+    if os.path.exists("/dev/nvidiactl"):
+        pytest.skip("the no-device half of this test needs a box without a GPU")
+    r = subprocess.run([exe, "test_sphere", "32", "16", "1", os.path.join(repo, "assets"), str(tmp_path / "o.png")],
+                       capture_output=True, text=True)
+    assert r.returncode == 1 and "rt_scene_create" in r.stderr and "failed: -2" in r.stderr, (r.returncode, r.stderr)
+    assert not (tmp_path / "o.png").exists()
