@@ -46,6 +46,18 @@ namespace rtb {
 #ifndef RT_CTA_MIN_BLOCKS
 #define RT_CTA_MIN_BLOCKS 2  // register cap 85 (80 used): fits traversal and the common shading classes
 #endif
+// Traverse phase: 1 = scattered rays and camera rays share ONE instance of the traversal loop.  The media sets inline
+// a medium test into every leaf visit: one instance instead of two takes 2 100 instructions (34 KB) out of the
+// kernel and its spills from 56 to 8 B — cornell_box +6.6 %, final_scene +4.9 % (the instruction cache was the
+// issue: `no_instruction` 0.95 cycles per issue).  The other sets keep the two specialised loops (one loop:
+// -2.2 % cover_100k_motion, -1.5 % simple_light_scene, +-0.3 % cover scene).
+#ifndef RT_CTA_ONE_LOOP
+#if defined(RT_CTA_F) && ((RT_CTA_F) & 2)
+#define RT_CTA_ONE_LOOP 1
+#else
+#define RT_CTA_ONE_LOOP 0
+#endif
+#endif
 #ifndef RT_CTA_PROFILE
 #define RT_CTA_PROFILE 0  // development: phase / work cycle counters into stats[8..13] (class_counts of RtStats)
 #endif
@@ -322,6 +334,54 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
             L.xc.chain = 0;
             L.xc.ro = L.ray;
             L.rng.state = 0;
+#if RT_CTA_ONE_LOOP
+            // One instance of the traversal loop serves both parts of the todo list (instruction-cache footprint):
+            // stage 0 = scattered rays, idle lanes refilled from the block's counter; stage 1 = camera rays, a
+            // coherent chunk of 32 neighbouring pixels at a time, run to completion.  `stage` is warp-uniform.
+            bool more = n_surv != 0u;
+            uint32_t stage = more ? 0u : 1u;
+            for (;;) {
+                if (L.pid != CTA_NONE && L.ts.cur == TRAV_NONE) cta_retire<F>(P, L, s_cnt);
+                uint32_t idx = CTA_NONE;  // todo entry this lane fetches now
+                if (stage == 0u) {
+                    if (more) {
+                        const uint32_t wm = __ballot_sync(0xffffffffu, L.pid == CTA_NONE);
+                        if (wm != 0u) {
+                            uint32_t base = 0;
+                            if (lane == 0) base = atomicAdd(&s_next, (uint32_t)__popc(wm));
+                            base = __shfl_sync(0xffffffffu, base, 0);
+                            if (base + (uint32_t)__popc(wm) >= n_surv) more = false;
+                            const uint32_t i = base + (uint32_t)__popc(wm & ((1u << lane) - 1u));
+                            if (L.pid == CTA_NONE && i < n_surv) idx = i;
+                        }
+                    }
+                    if (!__any_sync(0xffffffffu, L.pid != CTA_NONE || idx != CTA_NONE)) stage = 1u;  // scattered part drained
+                }
+                if (stage == 1u) {  // every lane is idle here
+                    uint32_t base = 0;
+                    if (lane == 0) base = atomicAdd(&s_nextp, 32u);
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    if (base >= n_regen) break;
+                    if (base + lane < n_regen) idx = n_surv + base + lane;
+                }
+                if (idx != CTA_NONE) {
+                    cta_fetch<F>(P, P.todo[idx], L);
+                    n_rays++;
+                }
+                // ---- traverse until enough lanes are idle again (stage 0, while there is something to refill them
+                //      with) or until the whole warp is done
+                for (;;) {
+                    while (!(L.ts.cur & LEAF_FLAG) && L.ts.cur != TRAV_NONE) node_visit<COUNT>(sc, L.rs, 1e-3f, L.ts, stack, &tc);
+                    if (L.ts.cur != TRAV_NONE) {
+                        leaf_visit<F, COUNT>(sc, L.ray, 1e-3f, L.ts, L.xc, L.rng, false, &tc);
+                        L.ts.pop(stack);
+                    }
+                    const uint32_t busy = __ballot_sync(0xffffffffu, L.ts.cur != TRAV_NONE);
+                    if (busy == 0u) break;
+                    if (stage == 0u && more && 32u - (uint32_t)__popc(busy) >= a.refill_idle) break;
+                }
+            }
+#else
             // ---- A2: scattered rays (incoherent): idle lanes are refilled from the block's counter
             bool more = n_surv != 0u;  // the todo list may still hold entries nobody has looked at (warp-uniform)
             for (;;) {
@@ -371,6 +431,7 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
                 }
                 __syncwarp();
             }
+#endif
         }
 #if RT_CTA_PROFILE
         if (lane == 0) pf_work[0] += clock64() - pf_t;
