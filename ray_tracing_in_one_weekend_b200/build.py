@@ -22,6 +22,7 @@ CXX = os.environ.get("CXX", "g++")
 HOST_SRCS = ["scene_api.cpp", "demo_scene.cpp", "bvh_build.cpp", "png_writer.cpp"]
 CUDA_SRCS = ["rtgpu.cu", "gpu_bvh.cu"]
 CTA_FEATURE_SETS = [0, 4, 8, 9, 11, 15]  # cta_inst.cu is compiled once per set (kernels_cta.cuh)
+CTA_NO_PBR_SETS = [0, 4]  # ... and once more without the pbr.rs shading class for the sphere-only sets
 HEADERS = ["scene_api.hpp", "bvh_build.hpp", "device_types.h", "rt_device.cuh", "kernels.cuh", "kernels_cta.cuh", "gpu_bvh.hpp",
            os.path.join("..", "..", "include", "rtgpu.h")]
 
@@ -67,6 +68,11 @@ def build_all(force: bool = False, verbose: bool = False) -> str:
         obj = os.path.join(CSRC, f"cta_f{f}.o")
         if force or _stale(obj, [os.path.join(CSRC, "cta_inst.cu")] + hdrs):
             jobs.append([NVCC] + NVCC_FLAGS + [f"-DRT_CTA_F={f}", "-c", "cta_inst.cu", "-o", obj])
+        objs.append(obj)
+    for f in CTA_NO_PBR_SETS:
+        obj = os.path.join(CSRC, f"cta_f{f}_m3f.o")
+        if force or _stale(obj, [os.path.join(CSRC, "cta_inst.cu")] + hdrs):
+            jobs.append([NVCC] + NVCC_FLAGS + [f"-DRT_CTA_F={f}", "-DRT_CTA_CLS_MASK=0x3f", "-DRT_CTA_SUFFIX=_m3f", "-c", "cta_inst.cu", "-o", obj])
         objs.append(obj)
     if jobs:  # the CUDA units are independent: compile them side by side
         from concurrent.futures import ThreadPoolExecutor

@@ -860,7 +860,8 @@ int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* c
         const bool media = (s->features & F_MEDIA) != 0;
         a.stage_perlin = !media && (s->class_mask >> CLS_DIFFUSE_PERLIN & 1u) && s->ds.n_perlin > 0 ? 1u : 0u;
         int threads = 0;
-        void* fn = cta_kernel_for(s->features, count, nullptr, &threads);
+        // (RT_CTA_FULL_KERNEL=1, development: always the build with every shading class)
+        void* fn = cta_kernel_for(s->features, env_int("RT_CTA_FULL_KERNEL", 0) ? 0x7fu : s->class_mask, count, nullptr, &threads);
         const int dflt_paths = a.stage_perlin ? 1120 : 1152;
         a.n_paths = (uint32_t)std::max(32, std::min(4096, env_int("RT_CTA_PATHS", dflt_paths))) & ~31u;
         a.refill_idle = (uint32_t)std::max(1, std::min(32, env_int("RT_CTA_REFILL", 8)));

@@ -30,6 +30,10 @@ for f in b.CTA_FEATURE_SETS:  # the CTA renderer lives in its own translation un
     o = os.path.join(os.path.abspath(out), f"cta_f{f}.o")
     subprocess.check_call([b.NVCC] + [x for x in b.NVCC_FLAGS if x not in ("-Xptxas", "-v")] + extra + [f"-DRT_CTA_F={f}", "-c", "cta_inst.cu", "-o", o], cwd=b.CSRC)
     objs.append(o)
+for f in b.CTA_NO_PBR_SETS:
+    o = os.path.join(os.path.abspath(out), f"cta_f{f}_m3f.o")
+    subprocess.check_call([b.NVCC] + [x for x in b.NVCC_FLAGS if x not in ("-Xptxas", "-v")] + extra + [f"-DRT_CTA_F={f}", "-DRT_CTA_CLS_MASK=0x3f", "-DRT_CTA_SUFFIX=_m3f", "-c", "cta_inst.cu", "-o", o], cwd=b.CSRC)
+    objs.append(o)
 subprocess.check_call([b.NVCC, "-shared", "-o", os.path.join(out, "librtgpu.so")] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lz"])
 os.remove(obj)
 print(os.path.join(out, "librtgpu.so"))
