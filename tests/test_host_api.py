@@ -216,3 +216,52 @@ def test_header_is_plain_c99_and_the_c_example_links(rtlib, tmp_path):
                        capture_output=True, text=True)
     assert r.returncode == 1 and "rt_scene_create" in r.stderr and "failed: -2" in r.stderr, (r.returncode, r.stderr)
     assert not (tmp_path / "o.png").exists()
+
+
+def _synthetic_flat(api, mats, prim_mats, radii):
+    """A minimal RtFlatScene: one ConstantTex, the given materials (kind per entry), one sphere per prim_mats entry."""
+    tex = (api.RtTexture * 1)()
+    tex[0].kind = 0
+    m = (api.RtMaterial * len(mats))()
+    for i, k in enumerate(mats):
+        m[i].kind, m[i].tex0 = k, 0
+    p = (api.RtPrim * len(prim_mats))()
+    for i, (mi, r) in enumerate(zip(prim_mats, radii)):
+        p[i].kind, p[i].mat = 0, mi  # RT_PRIM_SPHERE
+        p[i].g[0], p[i].g[1], p[i].g[2], p[i].g[3] = float(i), 0.0, 0.0, r
+    f = api.RtFlatScene()
+    f.abi_version = 1
+    f.n_prims, f.n_materials, f.n_textures = len(prim_mats), len(mats), 1
+    f.prims, f.materials, f.textures = p, m, tex
+    return f, (tex, m, p)
+
+
+def test_shade_queues_synthetic_edge_cases(rtlib):
+    """More kinds than queues (the lightest pbr.rs kinds share the class queue, the heaviest by surface get their
+    own), an unreferenced material (lands in its class's queue), a bad material index (error code, no crash)."""
+    api = rtlib.api
+    lib = rtlib.load_library()
+    # materials: Diffuse, Metal, then seven pbr.rs kinds (6..12) and one unreferenced Dielectric
+    mats = [1, 3, 6, 7, 8, 9, 10, 11, 12, 4]
+    prim_mats = [0, 1, 2, 3, 4, 5, 6, 7, 8]
+    radii = [1.0, 1.0, 9.0, 8.0, 7.0, 0.3, 0.2, 0.1, 0.05]
+    f, keep = _synthetic_flat(api, mats, prim_mats, radii)
+    mq = (C.c_uint8 * len(mats))()
+    qc, qo = C.c_uint32(), C.c_uint32()
+    assert lib.rt_flat_shade_queues(C.byref(f), mq, C.byref(qc), C.byref(qo)) == 0
+    mq = list(mq)
+    q_cls = [(qc.value >> (4 * q)) & 15 for q in range(7)]
+    # classes in use: Diffuse(Constant)=1, Metal=2, pbr=6 -> 3 queues, 3 free ones go to the three largest pbr kinds
+    assert sorted(q_cls[1:]) == [1, 2, 6, 6, 6, 6]
+    own = [mq[2], mq[3], mq[4]]                     # radii 9, 8, 7
+    assert len(set(own)) == 3 and all(q_cls[q] == 6 for q in own)
+    shared = {mq[i] for i in (5, 6, 7, 8)}          # the four small ones share the class queue
+    assert len(shared) == 1 and shared.isdisjoint(own) and q_cls[shared.pop()] == 6
+    assert q_cls[mq[0]] == 1 and q_cls[mq[1]] == 2
+    assert mq[9] == 0 or q_cls[mq[9]] == 3          # unreferenced Dielectric: no queue of its class exists -> 0
+    # pbr queues come before Diffuse and Metal in the drain order (numbered by cost)
+    assert max(q for q in range(1, 7) if q_cls[q] == 6) < min(mq[0], mq[1])
+    # bad material index
+    f2, keep2 = _synthetic_flat(api, [1], [5], [1.0])
+    assert lib.rt_flat_shade_queues(C.byref(f2), mq if False else (C.c_uint8 * 1)(), C.byref(qc), C.byref(qo)) < 0
+    assert b"material" in lib.rt_last_error()
