@@ -17,6 +17,12 @@
  *   - all geometry/shading arithmetic is IEEE binary32, in the reference's operation order.
  *   - there is NO CPU fallback: a call on a machine without a usable CUDA device fails with
  *     RT_ERR_CUDA.
+ *   - THREADING: a handle (RtScene, RtComm) allows ONE call in flight at a time — the per-scene statistics and
+ *     work counters are shared by its renders; different handles may be used from different threads.  The
+ *     reference's objects are Send + Sync and shared read-only across its workers (src/hitable.rs:50,
+ *     src/material.rs:10, src/texture.rs:11); its only mutable state is the per-thread RNG (src/lib.rs:7-9), which
+ *     becomes a per-path counter-seeded stream here.
+ *   - the library reads no environment variables.
  */
 #ifndef RTGPU_H
 #define RTGPU_H
@@ -28,14 +34,15 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 1u
+#define RT_ABI_VERSION 2u
 
 typedef enum RtStatus {
     RT_OK = 0,
     RT_ERR_ARG = -1,      /* bad argument / inconsistent scene description */
     RT_ERR_CUDA = -2,     /* CUDA runtime error (no device, OOM, launch failure) */
     RT_ERR_IO = -3,       /* asset file missing/unreadable (host scene builders), PNG file not writable */
-    RT_ERR_UNSUPPORTED = -4
+    RT_ERR_UNSUPPORTED = -4, /* a scene the backend cannot render the way the reference would (see rt_scene_create) */
+    RT_ERR_NCCL = -5      /* NCCL error (communicator setup, reduce) */
 } RtStatus;
 
 /* ------------------------------------------------------------------------------------------------
@@ -56,7 +63,10 @@ typedef enum RtPrimKind {
     RT_PRIM_MOVING_SPHERE = 4, /* EXTENSION (not in the reference snapshot; RTNW section 2)
                                   g = {c0.xyz, r, c1.xyz, time0, time1} */
     RT_PRIM_MEDIUM = 5         /* src/hitable.rs:523-588  g = {neg_inv_density};
-                                  aux0/aux1 = first/count of its boundary primitives */
+                                  aux0/aux1 = first/count of its boundary primitives (a HitableList, scanned in
+                                  order).  `xform` = the Translate/RotateY wrappers AROUND the medium; every boundary
+                                  primitive's chain starts with the same ops (a wrapper of the medium wraps its
+                                  boundary too) followed by the boundary's own wrappers. */
 } RtPrimKind;
 
 #define RT_PRIM_FLAG_BOUNDARY_ONLY 1u /* only reachable through a RT_PRIM_MEDIUM, not in the world */
@@ -197,11 +207,16 @@ typedef struct RtFlatScene {
  * ---------------------------------------------------------------------------------------------- */
 typedef struct RtScene RtScene; /* opaque: owns device memory, texture objects, streams */
 
-/* Uploads `desc` to CUDA device `device` (copies everything; the caller may free `desc` on return),
+/* Uploads `desc` to CUDA device `device` (copies everything; the caller may free `desc` on return) — every table
+ * in ONE device allocation filled by ONE host-to-device copy from a pinned staging buffer — and
  * builds the 4-wide BVH (128-byte, 32-byte-aligned nodes) over the world primitives: binned SAH on the host
  * below 32768 world primitives, LBVH on the device from there on (see rt_scene_create_ex).
  * Replaces: the scene hand-off `let (world, cam) = scene_fn(aspect)` + `build_bvh`
- * (src/main.rs:74, src/demo_scene.rs:223-227, src/hitable.rs:177-221). */
+ * (src/main.rs:74, src/demo_scene.rs:223-227, src/hitable.rs:177-221).
+ * RT_ERR_ARG: malformed description.  RT_ERR_UNSUPPORTED: a well-formed scene whose picture in the reference depends
+ * on STALE HitRecord fields (rects never write rec.tang, src/hitable.rs:262-269; media write
+ * neither uv nor tang, 568-576) — DisneyMetal on anything but a sphere, an Isotropic phase function with a
+ * uv-reading (image) texture on a medium — or a ConstantMedium whose boundary is itself a ConstantMedium. */
 int rt_scene_create(const RtFlatScene* desc, int device, RtScene** out);
 
 /* Same, with options.  RT_SCENE_GPU_BVH: build the acceleration structure ON THE DEVICE (Morton codes, radix
@@ -224,6 +239,13 @@ typedef struct RtBvhInfo {
     float build_ms;       /* wall clock of the build inside rt_scene_create */
 } RtBvhInfo;
 int rt_scene_bvh_info(const RtScene* scene, RtBvhInfo* out);
+
+/* The checks rt_scene_create runs on a description, without a device: RT_OK, RT_ERR_ARG or RT_ERR_UNSUPPORTED. */
+int rt_flat_validate(const RtFlatScene* desc);
+
+/* Device buffers and pinned host staging buffers are kept in a process-wide cache between calls (a host that
+ * creates a scene per frame does not pay the driver allocator every time); this frees whatever is idle. */
+void rt_release_cached_memory(void);
 
 /* Host-only planning step of rt_scene_create, exposed for inspection and tests (no device needed): how the
  * CTA-wavefront renderer's shade queues are assigned for this scene.  The renderer sorts the hits of an iteration
@@ -253,7 +275,8 @@ typedef struct RtHit {
 int rt_closest_hit(RtScene* scene, const float* o_xyz, const float* d_xyz, const float* times,
                    size_t n, float t_min, float t_max, RtHit* out);
 /* Same, all pointers are device pointers on the scene's device; asynchronous on `cuda_stream`
- * (a cudaStream_t passed as void*, NULL = the scene's own stream). */
+ * (a cudaStream_t passed as void*, NULL = the scene's own non-blocking stream; the legacy default stream is
+ * cudaStreamLegacy, i.e. (void*)0x1). */
 int rt_closest_hit_device(RtScene* scene, const float* o_xyz, const float* d_xyz,
                           const float* times, size_t n, float t_min, float t_max, RtHit* out,
                           void* cuda_stream);
@@ -264,10 +287,12 @@ int rt_camera_get_rays(const RtCamera* cam, const float* uv, size_t n, float* o_
 
 typedef enum RtRenderMode {
     RT_MODE_AUTO = 0,       /* = RT_MODE_CTA_WAVEFRONT, the fastest on every measured scene */
-    RT_MODE_MEGAKERNEL = 1, /* persistent per-thread path loop with in-warp path regeneration */
-    RT_MODE_WAVEFRONT = 2,  /* raygen / traverse / shade+compact kernels over ray queues in device memory */
-    RT_MODE_CTA_WAVEFRONT = 3 /* one persistent kernel; every thread block runs the wavefront loop on a
-                                 path pool and class queues held in its shared memory */
+    RT_MODE_MEGAKERNEL = 1, /* persistent per-thread path loop with in-warp path regeneration; kept as the
+                               independent cross-check of the default renderer (same rays, other scheduling) */
+    /* 2 was the global-memory wavefront renderer of ABI 1 (1.7x slower everywhere; removed) */
+    RT_MODE_CTA_WAVEFRONT = 3 /* one persistent kernel; every thread block runs the wavefront loop (regenerate,
+                                 traverse, material-sorted shade, compaction) on a path pool and queues held in
+                                 its shared memory */
 } RtRenderMode;
 
 typedef struct RtRenderParams {
@@ -316,9 +341,10 @@ typedef struct RtStats {
 int rt_render_device(RtScene* scene, const RtRenderParams* params, float* accum_sum_rgb,
                      void* cuda_stream, RtStats* stats);
 
-/* Host-buffer convenience: zero an internal accumulation buffer, render the sample range, divide
+/* Host-buffer call: zero an internal accumulation buffer, render the sample range, divide
  * by spp_total (src/main.rs:98) and copy the linear float image to `out_rgb_mean`
- * (width*height*3 floats).  No gamma, no quantisation. */
+ * (width*height*3 floats).  No gamma, no quantisation.  A page-locked `out_rgb_mean` (cudaMallocHost /
+ * cudaHostRegister) is written by one direct DMA; a pageable one through a pinned staging pipeline. */
 int rt_render(RtScene* scene, const RtRenderParams* params, float* out_rgb_mean, RtStats* stats);
 
 /* Reference output stage (src/main.rs:98-105,127): c = mean; c = c.powf(0.5); (c*255.99) as u8
@@ -330,6 +356,45 @@ int rt_resolve_rgb8(RtScene* scene, const float* rgb_mean, uint32_t width, uint3
  * image::save_buffer(file_name, &buf, nx, ny, ColorType::Rgb8) does at src/main.rs:128.
  * Host only (zlib deflate); RT_ERR_IO when the file cannot be written. */
 int rt_write_png(const char* path, const uint8_t* rgb8, uint32_t width, uint32_t height);
+
+/* ------------------------------------------------------------------------------------------------
+ * Multi-GPU: scene replicated, samples of every pixel partitioned over the ranks, ONE NCCL sum-reduce of the
+ * float32 accumulation buffers to rank 0 per frame (NVLink 5 / NVSwitch) — replaces the reference's mpsc gather
+ * of finished pixels (src/main.rs:72,101,114); paths are independent (src/main.rs:84-106), nothing else is
+ * exchanged.  Because a path's random stream depends only on (seed, pixel, global sample index), the N-GPU frame
+ * equals the 1-GPU frame up to float summation order.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct RtComm RtComm; /* opaque: owns one NCCL communicator per local device */
+#define RT_COMM_UNIQUE_ID_BYTES 128
+
+/* Global sample indices [*out_begin, *out_end) rank `rank` of `n_ranks` renders out of [sample_begin, sample_end):
+ * the ranges tile the interval, sizes differ by at most one. */
+int rt_partition_samples(uint32_t sample_begin, uint32_t sample_end, int n_ranks, int rank,
+                         uint32_t* out_begin, uint32_t* out_end);
+
+/* One process per GPU: rank 0 calls rt_comm_unique_id and ferries the 128 bytes to the other ranks by whatever
+ * means the launcher has (a file, MPI, torch.distributed); then EVERY rank calls rt_comm_create (collective). */
+int rt_comm_unique_id(uint8_t out_id[RT_COMM_UNIQUE_ID_BYTES]);
+int rt_comm_create(const uint8_t id[RT_COMM_UNIQUE_ID_BYTES], int n_ranks, int rank, int device, RtComm** out);
+/* One process that drives n devices (ncclCommInitAll): local device i is rank i. */
+int rt_comm_create_all(const int* devices, int n_devices, RtComm** out);
+int rt_comm_info(const RtComm* comm, int* n_ranks, int* first_rank, int* n_local);
+void rt_comm_destroy(RtComm* comm);
+
+/* One frame on all ranks.  `frame` describes the WHOLE frame: [sample_begin, sample_end) is split with
+ * rt_partition_samples, spp_total is the divisor.  scenes[i] (i < n_local) is the replica on the communicator's
+ * local device i.  Every rank renders its share into a zeroed sum buffer, one ncclReduce(sum, f32, root 0) follows
+ * on the same stream, rank 0 divides by spp_total and the process that owns rank 0 receives the linear float image
+ * in `out_rgb_mean` (host memory, width*height*3; ignored on the other processes).  Collective: every process of the
+ * communicator must make the call.  `stats` (optional) covers this process's ranks. */
+int rt_render_reduce(RtScene* const* scenes, RtComm* comm, const RtRenderParams* frame, float* out_rgb_mean,
+                     RtStats* stats);
+/* Same without the host copy: accum[i] are caller-owned DEVICE buffers (width*height*3 floats on local device i,
+ * overwritten); streams[i] (cudaStream_t as void*; NULL array or NULL entry = the scene's own stream) carry the
+ * memset, the render kernel, the reduce and, on rank 0, the division.  Asynchronous.  On return from the stream,
+ * accum of rank 0 holds the frame's mean. */
+int rt_render_reduce_device(RtScene* const* scenes, RtComm* comm, const RtRenderParams* frame,
+                            float* const* accum, void* const* streams);
 
 /* FP32 issue-rate microbenchmark (dependent-free FFMA chains on every SM): returns measured
  * lane-FFMA/s — the measured denominator of the instruction-issue roofline. */

@@ -119,6 +119,26 @@ void orc_camera_get_rays(const RtCamera* cam, const float* uv, size_t n, float* 
         put3(d + 3 * i, r.d);
     }
 }
+// SKY_COLOR of the scene (lib.rs:11; demo_scene.rs:22-35), incl. the env-map sky with its image
+int orc_scene_sky(OrcScene* s, const float d[3], float out[3]) {
+    if (!s) return -1;
+    put3(out, s->sc->sky(v3(d)));
+    return 0;
+}
+// First gradients / permutation entries of a freshly built Perlin table (texture.rs:60-91) drawn from
+// SmallRng::seed_from_u64(seed): rand_vec[0..n_vec) as xyz triples, perm_x/perm_y/perm_z[0..n_perm).
+void orc_perlin_table(uint64_t seed, uint32_t n_vec, float* rand_vec, uint32_t n_perm, uint32_t* px, uint32_t* py, uint32_t* pz) {
+    SmallRng saved = RNG();
+    RNG() = SmallRng::seed_from_u64(seed);
+    Perlin p;
+    RNG() = saved;
+    for (uint32_t i = 0; i < n_vec && i < 256; i++) put3(rand_vec + 3 * i, p.rand_vec[i]);
+    for (uint32_t i = 0; i < n_perm && i < 256; i++) {
+        px[i] = (uint32_t)p.perm_x[i];
+        py[i] = (uint32_t)p.perm_y[i];
+        pz[i] = (uint32_t)p.perm_z[i];
+    }
+}
 // Perlin noise / turbulence of texture `tex_id` (a PerlinTex) of a from-flat scene
 int orc_texture_value(OrcScene* s, uint32_t tex_id, const float uv[2], const float p[3], float out[3]) {
     if (!s || tex_id >= s->sc->texs.size()) return -1;
@@ -175,6 +195,78 @@ int orc_closest_hit(OrcScene* s, const float* o, const float* d, const float* ti
         out[i] = h;
     }
     media_disabled() = false;
+    return 0;
+}
+
+// world.hit with the media INCLUDED; every gen::<f32>() of ray i returns xi[i] (a constant injected sequence, so the
+// result does not depend on the order in which a traversal meets several media).
+int orc_closest_hit_xi(OrcScene* s, const float* o, const float* d, const float* xi, size_t n, float t_min, float t_max, RtHit* out) {
+    if (!s) return -1;
+    SmallRng saved = RNG();
+    float seq[256];
+    for (size_t i = 0; i < n; i++) {
+        for (float& v : seq) v = xi[i];
+        RNG().inject = seq;
+        RNG().inject_n = 256;
+        RNG().inject_i = 0;
+        Ray r{v3(o + 3 * i), v3(d + 3 * i), Vec2{}, 0.0f};
+        HitRecord rec;
+        RtHit h{};
+        if (s->sc->world.hit(r, t_min, t_max, rec)) {
+            h.prim = rec.prim;
+            h.t = rec.t;
+            put3(h.p, rec.p);
+            put3(h.n, rec.norm);
+            h.uv[0] = rec.uv.x;
+            h.uv[1] = rec.uv.y;
+            h.front_face = rec.front_face ? 1u : 0u;
+        } else {
+            h.prim = -1;
+        }
+        out[i] = h;
+    }
+    RNG() = saved;
+    return 0;
+}
+
+// ConstantMedium::hit (hitable.rs:536-579, through the Translate/RotateY wrappers around it) of world item
+// `item` — which must be the medium with flat primitive index `flat_prim` of a from-flat scene — with ONE injected
+// random number per case.  out per case (11 floats): hit, t, draws consumed, p[3], norm[3], front_face, 0
+int orc_medium_cases(OrcScene* s, uint32_t flat_prim, const float* rays, const float* tmm, const float* xi, size_t n, float* out) {
+    if (!s) return -1;
+    const Hitable* item = nullptr;
+    for (const auto& it : s->sc->world.items) {  // find the world item whose innermost object is that medium
+        const Hitable* h = it.get();
+        for (;;) {
+            if (auto t = dynamic_cast<const Translate*>(h)) h = t->ptr.get();
+            else if (auto r = dynamic_cast<const RotateY*>(h)) h = r->ptr.get();
+            else break;
+        }
+        auto cm = dynamic_cast<const ConstantMedium*>(h);
+        if (cm && cm->id == (int)flat_prim) item = it.get();
+    }
+    if (!item) return -2;
+    SmallRng saved = RNG();
+    for (size_t i = 0; i < n; i++) {
+        float seq[4] = {xi[i], xi[i], xi[i], xi[i]};
+        RNG().inject = seq;
+        RNG().inject_n = 4;
+        RNG().inject_i = 0;
+        Ray r{v3(rays + 6 * i), v3(rays + 6 * i + 3), Vec2{}, 0.0f};
+        HitRecord rec;
+        float* q = out + 11 * i;
+        for (int k = 0; k < 11; k++) q[k] = 0.0f;
+        const bool hit = item->hit(r, tmm[2 * i], tmm[2 * i + 1], rec);
+        q[0] = hit ? 1.0f : 0.0f;
+        q[2] = (float)RNG().inject_i;
+        if (hit) {
+            q[1] = rec.t;
+            put3(q + 3, rec.p);
+            put3(q + 6, rec.norm);
+            q[9] = rec.front_face ? 1.0f : 0.0f;
+        }
+    }
+    RNG() = saved;
     return 0;
 }
 

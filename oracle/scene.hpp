@@ -208,13 +208,14 @@ inline void RotateY::flatten(Flattener& f, uint32_t xf, bool bo) const {
     ptr->flatten(f, f.push_chain(xf, op), bo);
 }
 inline void ConstantMedium::flatten(Flattener& f, uint32_t xf, bool bo) const {
+    // The wrappers around the medium (chain xf) wrap its boundary too: the boundary primitives carry xf followed
+    // by their own wrappers, the medium record carries xf (hitable.rs:404-436,486-505 over 536-579).
     Flattener::ObjScope s(f);
-    if (xf != 0 || bo) throw std::runtime_error("ConstantMedium under a transform / as a boundary is not supported");
     uint32_t first = (uint32_t)f.prims.size();
-    boundary->flatten(f, 0, true);
+    boundary->flatten(f, xf, true);
     uint32_t count = (uint32_t)f.prims.size() - first;
     float g[1] = {neg_inv_density};
-    id = (int)f.push_prim(RT_PRIM_MEDIUM, phase_fn, 0, false, g, 1);
+    id = (int)f.push_prim(RT_PRIM_MEDIUM, phase_fn, xf, bo, g, 1);
     f.prims[id].aux0 = first;
     f.prims[id].aux1 = count;
 }
@@ -328,19 +329,10 @@ inline std::unique_ptr<Scene> scene_from_flat(const RtFlatScene& fs) {
     for (uint32_t i = 0; i < fs.n_textures; i++) get_tex(i);
     sc->mats = mats;
     sc->texs = tex;
-    auto make_geom = [&](uint32_t i) -> HitPtr {
-        const RtPrim& p = fs.prims[i];
-        HitPtr h;
-        switch (p.kind) {
-            case RT_PRIM_SPHERE: { auto s = std::make_shared<Sphere>(v3(p.g), p.g[3], mats.at(p.mat)); s->id = (int)i; h = s; break; }
-            case RT_PRIM_MOVING_SPHERE: { auto s = std::make_shared<MovingSphere>(v3(p.g), v3(p.g + 4), p.g[7], p.g[8], p.g[3], mats.at(p.mat)); s->id = (int)i; h = s; break; }
-            case RT_PRIM_XYRECT: { auto s = std::make_shared<XYRect>(v3(p.g), v3(p.g + 3), mats.at(p.mat)); s->id = (int)i; h = s; break; }
-            case RT_PRIM_XZRECT: { auto s = std::make_shared<XZRect>(v3(p.g), v3(p.g + 3), mats.at(p.mat)); s->id = (int)i; h = s; break; }
-            case RT_PRIM_YZRECT: { auto s = std::make_shared<YZRect>(v3(p.g), v3(p.g + 3), mats.at(p.mat)); s->id = (int)i; h = s; break; }
-            default: throw std::runtime_error("bad prim kind");
-        }
-        const RtXformChain& ch = fs.xform_chains[p.xform];
-        for (int k = (int)ch.n_ops - 1; k >= 0; k--) {  // innermost wrapper first
+    // wraps `h` in the wrappers ops[first_op + skip .. first_op + n_ops) of chain `xf`, innermost first
+    auto wrap = [&](HitPtr h, uint32_t xf, uint32_t skip) -> HitPtr {
+        const RtXformChain& ch = fs.xform_chains[xf];
+        for (int k = (int)ch.n_ops - 1; k >= (int)skip; k--) {
             const RtXformOp& op = fs.xform_ops[ch.first_op + k];
             if (op.kind == RT_XF_TRANSLATE) {
                 h = std::make_shared<Translate>(v3(op.v), h);
@@ -353,21 +345,39 @@ inline std::unique_ptr<Scene> scene_from_flat(const RtFlatScene& fs) {
         }
         return h;
     };
+    auto make_geom = [&](uint32_t i, uint32_t skip) -> HitPtr {
+        const RtPrim& p = fs.prims[i];
+        HitPtr h;
+        switch (p.kind) {
+            case RT_PRIM_SPHERE: { auto s = std::make_shared<Sphere>(v3(p.g), p.g[3], mats.at(p.mat)); s->id = (int)i; h = s; break; }
+            case RT_PRIM_MOVING_SPHERE: { auto s = std::make_shared<MovingSphere>(v3(p.g), v3(p.g + 4), p.g[7], p.g[8], p.g[3], mats.at(p.mat)); s->id = (int)i; h = s; break; }
+            case RT_PRIM_XYRECT: { auto s = std::make_shared<XYRect>(v3(p.g), v3(p.g + 3), mats.at(p.mat)); s->id = (int)i; h = s; break; }
+            case RT_PRIM_XZRECT: { auto s = std::make_shared<XZRect>(v3(p.g), v3(p.g + 3), mats.at(p.mat)); s->id = (int)i; h = s; break; }
+            case RT_PRIM_YZRECT: { auto s = std::make_shared<YZRect>(v3(p.g), v3(p.g + 3), mats.at(p.mat)); s->id = (int)i; h = s; break; }
+            default: throw std::runtime_error("bad prim kind");
+        }
+        return wrap(h, p.xform, skip);
+    };
     for (uint32_t i = 0; i < fs.n_prims; i++) {
         const RtPrim& p = fs.prims[i];
         if (p.flags & RT_PRIM_FLAG_BOUNDARY_ONLY) continue;
         if (p.kind == RT_PRIM_MEDIUM) {
+            // boundary chains start with the medium's own chain: those ops wrap the medium, the rest the boundary
+            const uint32_t n_outer = fs.xform_chains[p.xform].n_ops;
             auto bl = std::make_shared<HitableList>();
-            for (uint32_t k = 0; k < p.aux1; k++) bl->items.push_back(make_geom(p.aux0 + k));
+            for (uint32_t k = 0; k < p.aux1; k++) {
+                if (fs.prims[p.aux0 + k].kind == RT_PRIM_MEDIUM) throw std::runtime_error("nested medium");
+                bl->items.push_back(make_geom(p.aux0 + k, n_outer));
+            }
             auto iso = std::dynamic_pointer_cast<Isotropic>(mats.at(p.mat));
             if (!iso) throw std::runtime_error("medium material must be Isotropic");
             auto cm = std::make_shared<ConstantMedium>(bl, 1.0f, iso->albedo);
             cm->phase_fn = iso;
             cm->neg_inv_density = p.g[0];
             cm->id = (int)i;
-            sc->world.items.push_back(cm);
+            sc->world.items.push_back(wrap(cm, p.xform, 0));
         } else {
-            sc->world.items.push_back(make_geom(i));
+            sc->world.items.push_back(make_geom(i, 0));
         }
     }
     sc->sky.kind = (SkyKind)fs.sky.kind;
@@ -668,6 +678,34 @@ inline std::unique_ptr<Scene> furnace(float aspect_ratio, const std::string& whi
     return sc;
 }
 
+// EXTENSION (see csrc/demo_scene.cpp smoke_instances): media under Translate / RotateY wrappers
+inline std::unique_ptr<Scene> smoke_instances(float aspect_ratio) {
+    auto sc = std::make_unique<Scene>();
+    sc->sky.kind = SkyKind::Black;
+    MatPtr red = mk<Diffuse>(ctex(0.65f, 0.05f, 0.05f));
+    MatPtr white = mk<Diffuse>(ctex(0.73f, 0.73f, 0.73f));
+    MatPtr green = mk<Diffuse>(ctex(0.12f, 0.45f, 0.15f));
+    MatPtr light = mk<Emission>(ctex(7, 7, 7));
+    HitPtr ball = mk<Translate>(Vec3A(400, 120, 200),
+                                mk<ConstantMedium>(mk<Sphere>(Vec3A(0, 0, 0), 100.0f, white), 0.02f, ctex(0.9f, 0.9f, 0.9f)));
+    HitPtr tall = mk<Translate>(Vec3A(265, 0, 295),
+                                mk<RotateY>(mk<ConstantMedium>(mk<GBox>(Vec3A(), Vec3A(165, 330, 165), white), 0.01f, ctex(0, 0, 0)), 15.0f));
+    HitPtr low = mk<RotateY>(mk<ConstantMedium>(mk<Translate>(Vec3A(60, 0, 130), mk<GBox>(Vec3A(), Vec3A(150, 150, 150), white)), 0.015f,
+                                                ctex(0.2f, 0.4f, 0.9f)), -10.0f);
+    std::vector<HitPtr> world = {
+        mk<XZRect>(Vec3A(113, 554, 127), Vec3A(443, 554, 432), light),
+        mk<XYRect>(Vec3A(0, 0, 555), Vec3A(555, 555, 555), white),
+        mk<XZRect>(Vec3A(0, 0, 0), Vec3A(555, 0, 555), white),
+        mk<XZRect>(Vec3A(0, 555, 0), Vec3A(555, 555, 555), white),
+        mk<YZRect>(Vec3A(0, 0, 0), Vec3A(0, 555, 555), red),
+        mk<YZRect>(Vec3A(555, 0, 0), Vec3A(555, 555, 555), green),
+        ball, tall, low,
+    };
+    sc->cam = Camera(Vec3A(278, 278, -800), Vec3A(278, 278, 0), Vec3A(0, 1, 0), 40.0f, aspect_ratio);
+    sc->world = build_bvh(world);
+    return sc;
+}
+
 inline std::unique_ptr<Scene> build_named_scene(const std::string& name, float aspect, const std::string& assets) {
     RNG() = SmallRng::seed_from_u64(1995);  // lib.rs:8 — the "main thread" generator of a fresh process
     if (name == "test_sphere") return test_sphere(aspect);
@@ -681,6 +719,7 @@ inline std::unique_ptr<Scene> build_named_scene(const std::string& name, float a
     if (name == "cornell_box_solid") return cornell_box(aspect, true);
     if (name == "final_scene") return final_scene(aspect, assets);
     if (name == "pbr_ibl") return pbr_ibl(aspect, assets);
+    if (name == "smoke_instances") return smoke_instances(aspect);
     if (name.rfind("furnace_", 0) == 0) return furnace(aspect, name.substr(8));
     throw std::runtime_error("unknown scene " + name);
 }

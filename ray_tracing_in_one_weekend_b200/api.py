@@ -13,10 +13,13 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 REPO = os.path.dirname(HERE)
-LIB_PATH = os.environ.get("RTGPU_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "librtgpu.so")  # RTGPU_LIB: development override
+LIB_PATH = os.environ.get("RTGPU_LIB") or os.path.join(HERE, "librtgpu.so")  # RTGPU_LIB: development override
+TEST_LIB_PATH = os.path.join(HERE, "librtgpu_test.so")  # product objects + rt_test_* hooks (tests only)
+RT_ERR_ARG, RT_ERR_CUDA, RT_ERR_IO, RT_ERR_UNSUPPORTED, RT_ERR_NCCL = -1, -2, -3, -4, -5
+COMM_UNIQUE_ID_BYTES = 128
 ASSET_DIR = os.path.join(REPO, "assets")
 
-RT_ABI_VERSION = 1
+RT_ABI_VERSION = 2
 
 # RtPrimKind
 PRIM_SPHERE, PRIM_XYRECT, PRIM_XZRECT, PRIM_YZRECT, PRIM_MOVING_SPHERE, PRIM_MEDIUM = range(6)
@@ -26,7 +29,7 @@ XF_TRANSLATE, XF_ROTATE_Y = 0, 1
  MAT_ROUGH_PLASTIC, MAT_DISNEY_DIFFUSE, MAT_DISNEY_METAL, MAT_DISNEY_SHEEN, MAT_DISNEY_CLEARCOAT) = range(13)
 TEX_CONSTANT, TEX_CHECKER, TEX_PERLIN, TEX_IMAGE = range(4)
 SKY_GRADIENT, SKY_BLACK, SKY_ENVMAP, SKY_CONSTANT = range(4)
-MODE_AUTO, MODE_MEGAKERNEL, MODE_WAVEFRONT, MODE_CTA_WAVEFRONT = range(4)
+MODE_AUTO, MODE_MEGAKERNEL, MODE_CTA_WAVEFRONT = 0, 1, 3  # (2 was the global-memory wavefront renderer of ABI 1)
 RENDER_COUNTERS = 1
 RENDER_RUSSIAN_ROULETTE = 2
 RENDER_COSINE_SAMPLING = 4
@@ -129,21 +132,16 @@ EXPORTED_SYMBOLS = [
     "rt_scene_create", "rt_scene_create_ex", "rt_scene_destroy", "rt_scene_bvh_info", "rt_closest_hit", "rt_closest_hit_device",
     "rt_camera_get_rays", "rt_render_device", "rt_render", "rt_resolve_rgb8", "rt_write_png", "rt_measure_fp32_peak",
     "rt_flat_shade_queues", "rt_last_error", "rt_host_scene_build", "rt_host_scene_flat", "rt_host_scene_destroy",
+    "rt_flat_validate", "rt_release_cached_memory", "rt_partition_samples", "rt_comm_unique_id", "rt_comm_create",
+    "rt_comm_create_all", "rt_comm_info", "rt_comm_destroy", "rt_render_reduce", "rt_render_reduce_device",
 ]
 
 _lib: Optional[C.CDLL] = None
+_test_lib: Optional[C.CDLL] = None
 
 
-def load_library() -> C.CDLL:
-    """dlopen librtgpu.so (built in-tree by ray_tracing_in_one_weekend_b200.build). Fails loudly."""
-    global _lib
-    if _lib is not None:
-        return _lib
-    if not os.path.exists(LIB_PATH):
-        raise RtError(-2, f"{LIB_PATH} is missing — run `python -m ray_tracing_in_one_weekend_b200.build` "
-                          "(there is no CPU fallback)")
-    lib = C.CDLL(LIB_PATH)
-    vp, fp, u32, sz = C.c_void_p, C.POINTER(C.c_float), C.c_uint32, C.c_size_t
+def _declare(lib: C.CDLL) -> None:
+    vp, u32, sz = C.c_void_p, C.c_uint32, C.c_size_t
     lib.rt_last_error.restype = C.c_char_p
     lib.rt_scene_create.argtypes = [C.POINTER(RtFlatScene), C.c_int, C.POINTER(vp)]
     lib.rt_scene_create_ex.argtypes = [C.POINTER(RtFlatScene), C.c_int, C.c_uint32, C.POINTER(vp)]
@@ -151,6 +149,9 @@ def load_library() -> C.CDLL:
     lib.rt_scene_destroy.restype = None
     lib.rt_scene_bvh_info.argtypes = [vp, C.POINTER(RtBvhInfo)]
     lib.rt_flat_shade_queues.argtypes = [vp, C.POINTER(C.c_uint8), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+    lib.rt_flat_validate.argtypes = [C.POINTER(RtFlatScene)]
+    lib.rt_release_cached_memory.argtypes = []
+    lib.rt_release_cached_memory.restype = None
     lib.rt_closest_hit.argtypes = [vp, vp, vp, vp, sz, C.c_float, C.c_float, vp]
     lib.rt_closest_hit_device.argtypes = [vp, vp, vp, vp, sz, C.c_float, C.c_float, vp, vp]
     lib.rt_camera_get_rays.argtypes = [C.POINTER(RtCamera), vp, sz, vp, vp]
@@ -164,16 +165,54 @@ def load_library() -> C.CDLL:
     lib.rt_host_scene_flat.restype = C.POINTER(RtFlatScene)
     lib.rt_host_scene_destroy.argtypes = [vp]
     lib.rt_host_scene_destroy.restype = None
-    # test-only entry points (not part of rtgpu.h)
-    lib.rt_test_shade_cases.argtypes = [vp, vp, vp, vp, vp, u32, u32, vp]
-    lib.rt_test_texture_cases.argtypes = [vp, u32, vp, vp, u32, vp]
+    lib.rt_partition_samples.argtypes = [u32, u32, C.c_int, C.c_int, C.POINTER(u32), C.POINTER(u32)]
+    lib.rt_comm_unique_id.argtypes = [vp]
+    lib.rt_comm_create.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]
+    lib.rt_comm_create_all.argtypes = [C.POINTER(C.c_int), C.c_int, C.POINTER(vp)]
+    lib.rt_comm_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    lib.rt_comm_destroy.argtypes = [vp]
+    lib.rt_comm_destroy.restype = None
+    lib.rt_render_reduce.argtypes = [C.POINTER(vp), vp, C.POINTER(RtRenderParams), vp, C.POINTER(RtStats)]
+    lib.rt_render_reduce_device.argtypes = [C.POINTER(vp), vp, C.POINTER(RtRenderParams), C.POINTER(vp), C.POINTER(vp)]
+
+
+def load_library() -> C.CDLL:
+    """dlopen librtgpu.so (built in-tree by ray_tracing_in_one_weekend_b200.build). Fails loudly."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RtError(-2, f"{LIB_PATH} is missing — run `python -m ray_tracing_in_one_weekend_b200.build` "
+                          "(there is no CPU fallback)")
+    lib = C.CDLL(LIB_PATH)
+    _declare(lib)
     _lib = lib
     return lib
 
 
-def _check(rc: int) -> None:
+def load_test_library() -> C.CDLL:
+    """dlopen librtgpu_test.so: the SAME objects as librtgpu.so plus the rt_test_* parity hooks (csrc/test_hooks.cu).
+    A separate library instance: scene handles made through it must be used through it (`Scene(..., lib=...)`)."""
+    global _test_lib
+    if _test_lib is not None:
+        return _test_lib
+    if not os.path.exists(TEST_LIB_PATH):
+        raise RtError(-2, f"{TEST_LIB_PATH} is missing — run `python -m ray_tracing_in_one_weekend_b200.build`")
+    lib = C.CDLL(TEST_LIB_PATH)
+    _declare(lib)
+    vp, u32 = C.c_void_p, C.c_uint32
+    lib.rt_test_shade_cases.argtypes = [vp, vp, vp, vp, vp, u32, u32, vp]
+    lib.rt_test_texture_cases.argtypes = [vp, u32, vp, vp, u32, vp]
+    lib.rt_test_medium_cases.argtypes = [vp, u32, vp, vp, vp, u32, vp]
+    lib.rt_test_closest_hit_xi.argtypes = [vp, vp, vp, vp, u32, C.c_float, C.c_float, vp]
+    lib.rt_test_bvh_validate.argtypes = [C.POINTER(RtFlatScene), u32, C.POINTER(RtBvhInfo)]
+    _test_lib = lib
+    return lib
+
+
+def _check(rc: int, lib: Optional[C.CDLL] = None) -> None:
     if rc != 0:
-        raise RtError(rc, load_library().rt_last_error().decode("utf-8", "replace"))
+        raise RtError(rc, (lib or load_library()).rt_last_error().decode("utf-8", "replace"))
 
 
 def _ptr(a: Optional[np.ndarray]):
@@ -273,22 +312,22 @@ def pixel_center_uv(width: int, height: int) -> np.ndarray:
 class Scene:
     """Device scene handle (rt_scene_create). Requires a CUDA device."""
 
-    def __init__(self, flat_ptr, device: int = 0, flags: Optional[int] = None):
-        self._lib = load_library()
+    def __init__(self, flat_ptr, device: int = 0, flags: Optional[int] = None, lib: Optional[C.CDLL] = None):
+        self._lib = lib or load_library()
         h = C.c_void_p()
         if flags is None:
-            _check(self._lib.rt_scene_create(flat_ptr, device, C.byref(h)))
+            _check(self._lib.rt_scene_create(flat_ptr, device, C.byref(h)), self._lib)
         else:
-            _check(self._lib.rt_scene_create_ex(flat_ptr, device, flags, C.byref(h)))
+            _check(self._lib.rt_scene_create_ex(flat_ptr, device, flags, C.byref(h)), self._lib)
         self._h = h
         self.device = device
         self.camera = RtCamera.from_buffer_copy(bytes(flat_ptr.contents.camera))
 
     @classmethod
-    def from_name(cls, name: str, aspect_ratio: float, device: int = 0, flags: Optional[int] = None) -> "Scene":
+    def from_name(cls, name: str, aspect_ratio: float, device: int = 0, flags: Optional[int] = None, lib=None) -> "Scene":
         hs = HostScene(name, aspect_ratio)
         try:
-            return cls(hs.flat, device, flags)
+            return cls(hs.flat, device, flags, lib)
         finally:
             hs.close()
 
@@ -305,7 +344,7 @@ class Scene:
 
     def bvh_info(self) -> RtBvhInfo:
         info = RtBvhInfo()
-        _check(self._lib.rt_scene_bvh_info(self._h, C.byref(info)))
+        _check(self._lib.rt_scene_bvh_info(self._h, C.byref(info)), self._lib)
         return info
 
     def closest_hit(self, o: np.ndarray, d: np.ndarray, t_min: float = 1e-3, t_max: float = 3.4028234663852886e38,
@@ -318,7 +357,7 @@ class Scene:
             times = np.ascontiguousarray(times, dtype=np.float32)
         out = np.zeros(n, dtype=HIT_DTYPE)
         _check(self._lib.rt_closest_hit(self._h, _ptr(o), _ptr(d), _ptr(times), n, C.c_float(t_min), C.c_float(t_max),
-                                        _ptr(out)))
+                                        _ptr(out)), self._lib)
         return out
 
     def make_params(self, width: int, height: int, spp: int, *, sample_begin: int = 0,
@@ -333,7 +372,7 @@ class Scene:
         p = self.make_params(width, height, spp, **kw)
         out = np.empty((height, width, 3), np.float32)
         st = RtStats()
-        _check(self._lib.rt_render(self._h, C.byref(p), _ptr(out), C.byref(st)))
+        _check(self._lib.rt_render(self._h, C.byref(p), _ptr(out), C.byref(st)), self._lib)
         return out, st
 
     def render_device(self, params: RtRenderParams, accum_ptr: int, stream_ptr: int = 0, want_stats: bool = True):
@@ -341,7 +380,7 @@ class Scene:
         st = RtStats() if want_stats else None
         _check(self._lib.rt_render_device(self._h, C.byref(params), C.c_void_p(accum_ptr),
                                           C.c_void_p(stream_ptr) if stream_ptr else None,
-                                          C.byref(st) if st is not None else None))
+                                          C.byref(st) if st is not None else None), self._lib)
         return st
 
     @staticmethod
@@ -356,7 +395,7 @@ class Scene:
         mean = np.ascontiguousarray(mean, dtype=np.float32)
         h, w = mean.shape[:2]
         out = np.empty((h, w, 3), np.uint8)
-        _check(self._lib.rt_resolve_rgb8(self._h, _ptr(mean), w, h, _ptr(out)))
+        _check(self._lib.rt_resolve_rgb8(self._h, _ptr(mean), w, h, _ptr(out)), self._lib)
         return out
 
 
@@ -365,3 +404,84 @@ def measure_fp32_peak(device: int = 0):
     a, b = C.c_double(), C.c_double()
     _check(lib.rt_measure_fp32_peak(device, C.byref(a), C.byref(b)))
     return a.value, b.value
+
+
+def release_cached_memory() -> None:
+    load_library().rt_release_cached_memory()
+
+
+def partition_samples(sample_begin: int, sample_end: int, n_ranks: int, rank: int):
+    """rt_partition_samples: global sample indices [begin, end) of `rank` (host arithmetic, no device needed)."""
+    b, e = C.c_uint32(), C.c_uint32()
+    _check(load_library().rt_partition_samples(sample_begin, sample_end, n_ranks, rank, C.byref(b), C.byref(e)))
+    return b.value, e.value
+
+
+def flat_validate(flat_ptr) -> None:
+    """rt_flat_validate: raises RtError(RT_ERR_ARG | RT_ERR_UNSUPPORTED) exactly as rt_scene_create would."""
+    _check(load_library().rt_flat_validate(flat_ptr))
+
+
+class Comm:
+    """RtComm: the NCCL communicator(s) of the spp-partitioned multi-GPU frame (rt_comm_* / rt_render_reduce*)."""
+
+    def __init__(self, handle, lib):
+        self._h, self._lib = handle, lib
+
+    @staticmethod
+    def unique_id() -> bytes:
+        buf = (C.c_uint8 * COMM_UNIQUE_ID_BYTES)()
+        _check(load_library().rt_comm_unique_id(buf))
+        return bytes(buf)
+
+    @classmethod
+    def from_id(cls, uid: bytes, n_ranks: int, rank: int, device: int) -> "Comm":
+        """One process per GPU (collective: every rank calls it with rank 0's id)."""
+        lib = load_library()
+        if len(uid) != COMM_UNIQUE_ID_BYTES:
+            raise ValueError("unique id must be 128 bytes")
+        buf = (C.c_uint8 * COMM_UNIQUE_ID_BYTES).from_buffer_copy(uid)
+        h = C.c_void_p()
+        _check(lib.rt_comm_create(buf, n_ranks, rank, device, C.byref(h)))
+        return cls(h, lib)
+
+    @classmethod
+    def all_local(cls, devices) -> "Comm":
+        """One process that drives several devices (ncclCommInitAll)."""
+        lib = load_library()
+        arr = (C.c_int * len(devices))(*devices)
+        h = C.c_void_p()
+        _check(lib.rt_comm_create_all(arr, len(devices), C.byref(h)))
+        return cls(h, lib)
+
+    def info(self):
+        a, b, c = C.c_int(), C.c_int(), C.c_int()
+        _check(self._lib.rt_comm_info(self._h, C.byref(a), C.byref(b), C.byref(c)))
+        return {"n_ranks": a.value, "first_rank": b.value, "n_local": c.value}
+
+    def render_reduce(self, scenes, params: RtRenderParams, out: Optional[np.ndarray] = None, want_stats: bool = True):
+        """rt_render_reduce: `params` describes the WHOLE frame; returns RtStats of this process's ranks.  `out` is
+        the (H,W,3) float32 host image (required on the process that owns rank 0)."""
+        arr = (C.c_void_p * len(scenes))(*[s._h for s in scenes])
+        st = RtStats() if want_stats else None
+        _check(self._lib.rt_render_reduce(arr, self._h, C.byref(params), _ptr(out), C.byref(st) if st is not None else None))
+        return st
+
+    def render_reduce_device(self, scenes, params: RtRenderParams, accum_ptrs, stream_ptrs=None) -> None:
+        """rt_render_reduce_device: asynchronous on the given streams; rank 0's buffer holds the mean afterwards."""
+        n = len(scenes)
+        arr = (C.c_void_p * n)(*[s._h for s in scenes])
+        acc = (C.c_void_p * n)(*accum_ptrs)
+        sts = (C.c_void_p * n)(*stream_ptrs) if stream_ptrs is not None else None
+        _check(self._lib.rt_render_reduce_device(arr, self._h, C.byref(params), acc, sts))
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self._lib.rt_comm_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -15,15 +15,17 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "librtgpu.so")
+TEST_LIB = os.path.join(HERE, "librtgpu_test.so")  # the product objects + csrc/test_hooks.cu (rt_test_* entry points)
 
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 CXX = os.environ.get("CXX", "g++")
 
 HOST_SRCS = ["scene_api.cpp", "demo_scene.cpp", "bvh_build.cpp", "png_writer.cpp"]
-CUDA_SRCS = ["rtgpu.cu", "gpu_bvh.cu"]
+CUDA_SRCS = ["rtgpu.cu", "rt_comm.cu", "gpu_bvh.cu"]
+TEST_SRCS = ["test_hooks.cu"]
 CTA_FEATURE_SETS = [0, 4, 8, 9, 11, 15]  # cta_inst.cu is compiled once per set (kernels_cta.cuh)
 CTA_NO_PBR_SETS = [0, 4]  # ... and once more without the pbr.rs shading class for the sphere-only sets
-HEADERS = ["scene_api.hpp", "bvh_build.hpp", "device_types.h", "rt_device.cuh", "kernels.cuh", "kernels_cta.cuh", "gpu_bvh.hpp",
+HEADERS = ["scene_api.hpp", "bvh_build.hpp", "device_types.h", "rt_device.cuh", "kernels.cuh", "kernels_cta.cuh", "gpu_bvh.hpp", "rt_internal.hpp",
            os.path.join("..", "..", "include", "rtgpu.h")]
 
 HOST_FLAGS = ["-std=c++17", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-Wall"]
@@ -59,11 +61,12 @@ def build_all(force: bool = False, verbose: bool = False) -> str:
             log.append(_run([CXX] + HOST_FLAGS + ["-c", src, "-o", obj]))
         objs.append(obj)
     jobs = []
-    for src in CUDA_SRCS:
+    test_objs = []
+    for src in CUDA_SRCS + TEST_SRCS:
         obj = os.path.join(CSRC, src.replace(".cu", ".o"))
         if force or _stale(obj, [os.path.join(CSRC, src)] + hdrs):
             jobs.append([NVCC] + NVCC_FLAGS + ["-c", src, "-o", obj])
-        objs.append(obj)
+        (test_objs if src in TEST_SRCS else objs).append(obj)
     for f in CTA_FEATURE_SETS:
         obj = os.path.join(CSRC, f"cta_f{f}.o")
         if force or _stale(obj, [os.path.join(CSRC, "cta_inst.cu")] + hdrs):
@@ -78,8 +81,12 @@ def build_all(force: bool = False, verbose: bool = False) -> str:
         from concurrent.futures import ThreadPoolExecutor
         with ThreadPoolExecutor(max_workers=min(len(jobs), os.cpu_count() or 4)) as ex:
             log.extend(ex.map(_run, jobs))
-    if force or _stale(LIB, objs):
-        log.append(_run([NVCC, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lz"]))
+    # exports.map: the dynamic symbol table holds the rt_* entry points and nothing else (no C++ internals)
+    link = ["-gencode", "arch=compute_100a,code=sm_100a", "-lz", "-lnccl", "-Xlinker", "--version-script=" + os.path.join(CSRC, "exports.map")]
+    if force or _stale(LIB, objs + [os.path.join(CSRC, "exports.map")]):
+        log.append(_run([NVCC, "-shared", "-o", LIB] + objs + link))
+    if force or _stale(TEST_LIB, objs + test_objs + [os.path.join(CSRC, "exports.map")]):
+        log.append(_run([NVCC, "-shared", "-o", TEST_LIB] + objs + test_objs + link))
     out = "".join(log)
     if verbose and out:
         print(out)

@@ -234,6 +234,56 @@ SceneOut pbr_ibl(float aspect, const std::string& assets) {
 }
 
 // Furnace scenes for the statistical KAT K10: one convex sphere under a constant white sky.
+// EXTENSION scene for the positions the reference allows a ConstantMedium in (any Hitable wraps any Hitable,
+// hitable.rs:404-436,438-520,523-588) beyond what its own scenes use: media UNDER Translate / RotateY wrappers, a
+// boundary with wrappers of its own below such a medium, a sphere boundary.  The Cornell room of demo_scene.rs:112-148.
+SceneOut smoke_instances(float aspect) {
+    SceneOut s;
+    s.sky.kind = RT_SKY_BLACK;
+    Mat red = Diffuse(rgb(0.65f, 0.05f, 0.05f));
+    Mat white = Diffuse(rgb(0.73f, 0.73f, 0.73f));
+    Mat green = Diffuse(rgb(0.12f, 0.45f, 0.15f));
+    Mat light = Emission(rgb(7, 7, 7));
+    // Translate(ConstantMedium(Sphere))
+    Hit ball = Translate(V3(400, 120, 200), ConstantMedium(Sphere(V3(0, 0, 0), 100.0f, white), 0.02f, rgb(0.9f, 0.9f, 0.9f)));
+    // Translate(RotateY(ConstantMedium(GBox))): the boundary sits directly below the medium
+    Hit tall = Translate(V3(265, 0, 295), RotateY(ConstantMedium(GBox(V3(0, 0, 0), V3(165, 330, 165), white), 0.01f, rgb(0, 0, 0)), 15.0f));
+    // RotateY(ConstantMedium(Translate(GBox))): the boundary carries a wrapper of its own below the medium
+    Hit low = RotateY(ConstantMedium(Translate(V3(60, 0, 130), GBox(V3(0, 0, 0), V3(150, 150, 150), white)), 0.015f, rgb(0.2f, 0.4f, 0.9f)), -10.0f);
+    HitableList world = {
+        XZRect(V3(113, 554, 127), V3(443, 554, 432), light),
+        XYRect(V3(0, 0, 555), V3(555, 555, 555), white),
+        XZRect(V3(0, 0, 0), V3(555, 0, 555), white),
+        XZRect(V3(0, 555, 0), V3(555, 555, 555), white),
+        YZRect(V3(0, 0, 0), V3(0, 555, 555), red),
+        YZRect(V3(555, 0, 0), V3(555, 555, 555), green),
+        ball, tall, low,
+    };
+    s.cam = Camera(V3(278, 278, -800), V3(278, 278, 0), V3(0, 1, 0), 40.0f, aspect);
+    s.world = build_bvh(world);
+    return s;
+}
+
+// Well-formed scenes the backend must REFUSE (RT_ERR_UNSUPPORTED) because the reference's picture of them depends on
+// stale HitRecord fields (quirk A4) or on a stochastic boundary: used by the validation tests.
+SceneOut unsupported_scene(float aspect, const std::string& which, const std::string& assets) {
+    SceneOut s;
+    s.sky.kind = RT_SKY_GRADIENT;
+    Mat white = Diffuse(rgb(0.73f, 0.73f, 0.73f));
+    if (which == "nested_medium") {
+        Hit inner = ConstantMedium(Sphere(V3(0, 0, -1), 0.5f, white), 1.0f, rgb(1, 1, 1));
+        s.world = {ConstantMedium(inner, 1.0f, rgb(1, 1, 1))};
+    } else if (which == "disney_metal_rect") {
+        s.world = {XYRect(V3(-1, -1, -2), V3(1, 1, -2), DisneyMetal(rgb(0.6f, 0.5f, 0.4f), 0.4f, 0.5f, 0.1f))};
+    } else if (which == "image_isotropic_medium") {
+        s.world = {ConstantMedium(Sphere(V3(0, 0, -1), 0.5f, white), 1.0f, ImageTexFromPpm(assets + "/earthmap.ppm"))};
+    } else {
+        throw std::runtime_error("unknown unsupported-scene " + which);
+    }
+    s.cam = Camera(V3(0, 0, 0), V3(0, 0, -1), V3(0, 1, 0), 90.0f, aspect);
+    return s;
+}
+
 SceneOut furnace(float aspect, const std::string& which) {
     SceneOut s;
     s.sky.kind = RT_SKY_CONSTANT;
@@ -273,6 +323,8 @@ std::unique_ptr<FlatSceneOwner> build_named_scene(const std::string& name, float
     else if (name == "cornell_box_solid") s = cornell_box(aspect, true);
     else if (name == "final_scene") s = final_scene(aspect, assets);
     else if (name == "pbr_ibl") s = pbr_ibl(aspect, assets);
+    else if (name == "smoke_instances") s = smoke_instances(aspect);
+    else if (name.rfind("unsupported_", 0) == 0) s = unsupported_scene(aspect, name.substr(12), assets);
     else if (name.rfind("furnace_", 0) == 0) s = furnace(aspect, name.substr(8));
     else throw std::runtime_error("unknown scene '" + name + "'");
     return flatten(s.world, s.cam, s.sky);

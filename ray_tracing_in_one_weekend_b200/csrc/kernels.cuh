@@ -160,410 +160,6 @@ __global__ void __launch_bounds__(MEGA_THREADS) k_render_mega(DeviceScene sc, Re
     }
 }
 
-// ======================================================================================= wavefront
-// Wavefront path tracer: a pool of P path slots lives in device memory (SoA, 64 B per path, sized to
-// stay L2-resident); every iteration advances every live path by one ray with these kernels:
-//
-//   k_wf_traverse<F>     PERSISTENT warps.  Each lane owns one ray at a time; a warp takes slot indices
-//                        from a global counter in chunks (one atomic per chunk), and whenever
-//                        fewer than `refill_threshold` lanes are still traversing it retires the finished
-//                        lanes and refills them from its chunk (Aila & Laine 2009 "dynamic fetch"), so SIMT
-//                        lanes stay busy although rays need 1..15 node visits.  A retired ray is binned by
-//                        SHADING CLASS (miss / per material group; the class comes with the primitive
-//                        record) into a per-warp shared-memory staging buffer that is flushed WF_FLUSH
-//                        slot ids at a time (ballot/popc ranks, one global atomic per flush) into that
-//                        class's queue.
-//   k_wf_shade<F, CLS>   one kernel per shading class present in the scene (material-sorted shading, class
-//                        code only): sky / emitted / scatter, radiance accumulation, writes the scattered
-//                        ray back into the slot and REGENERATES a fresh camera path in place when the path
-//                        ended (so the pool stays full and no compaction pass is needed until the frame
-//                        drains).  The class kernels of one iteration are independent graph nodes.
-//
-// Replaces main.rs:38-60,84-97 exactly like the megakernel (same device functions, same RNG streams:
-// a path's stream depends only on (seed, pixel, global sample index)).
-constexpr int WF_NCLASS = 8;  // queues 0..CLS_COUNT-1; counter [7] = rays traced this iteration
-constexpr int WF_TRAV_THREADS = 128;
-constexpr int WF_TRAV_WARPS = WF_TRAV_THREADS / 32;
-constexpr int WF_SHADE_THREADS = 128;
-constexpr uint32_t WF_FLUSH = 64;   // staged slot ids written per queue flush
-constexpr uint32_t WF_STAGE = 96;   // staging capacity per (warp, class): < WF_FLUSH pending + 32 appended
-static_assert(CLS_COUNT <= WF_NCLASS - 1, "class queues");
-
-// Per-frame parameters live in device memory so that the kernel arguments (and therefore the CUDA graph
-// of one iteration) stay the same from frame to frame.
-struct WfFrame {
-    float* accum;
-    uint32_t width, height;
-    uint32_t s_begin, n_samples, max_depth, refill_threshold;
-    uint32_t chunk, pad0;  // slot indices a traverse warp reserves per atomic
-    uint64_t seed;
-    unsigned long long total_paths;  // width * height * n_samples
-};
-
-struct WfArgs {
-    float4* ray_o;   // o.xyz, time
-    float4* ray_d;   // d.xyz, bits(depth | alive << 31)
-    float4* beta;    // throughput rgb, bits(pixel)
-    uint2* rng;      // PCG state
-    uint2* hit;      // bits(t), device prim (0xffffffff = miss)
-    uint32_t* queue; // CLS_COUNT segments of P slot ids
-    uint32_t* n_class;       // [2][WF_NCLASS] double-buffered per-class counts; [.][7] = rays traced
-    uint32_t* trav_counter;  // [2] next unreserved slot index of the traverse kernel
-    unsigned long long* path_counter;
-    unsigned long long* stats;  // [0] rays [1] shade calls [2..4] counters
-    const WfFrame* frame;
-    uint32_t P;
-};
-
-constexpr uint32_t WF_NO_SLOT = 0xffffffffu;
-
-// New camera path for a slot (main.rs:88-93).  Path index k -> (sample, pixel): k = s * (W*H) + pixel, pixels
-// row-major, so the 32 lanes of a warp start on 32 neighbouring pixels of one row with the same sample index.
-RT_DEV void wf_generate(const DeviceScene& sc, const WfFrame& f, unsigned long long k, Ray& ray, V3f& beta, uint32_t& pixel,
-                        PcgRng& rng) {
-    const unsigned long long per_sample = (unsigned long long)f.width * f.height;
-    const uint32_t s = f.s_begin + (uint32_t)(k / per_sample);
-    pixel = (uint32_t)(k % per_sample);
-    const uint32_t py = pixel / f.width, px = pixel - py * f.width;
-    rng.seed(f.seed, pixel, s);
-    float u = ((float)px + rng.next()) / (float)f.width;
-    float v = ((float)py + rng.next()) / (float)f.height;
-    ray = camera_get_ray(sc.cam, u, v, rng);
-    beta = mk3(1.0f, 1.0f, 1.0f);
-}
-
-// Warp-aggregated fetch of new path indices for the lanes with `want` set. Returns k (or ~0 when none left).
-RT_DEV unsigned long long wf_fetch(const WfArgs& a, bool want) {
-    const uint32_t mask = __ballot_sync(0xffffffffu, want);
-    if (mask == 0) return ~0ull;
-    const uint32_t lane = threadIdx.x & 31u;
-    const int leader = __ffs(mask) - 1;
-    unsigned long long base = 0;
-    if ((int)lane == leader) base = atomicAdd(a.path_counter, (unsigned long long)__popc(mask));
-    base = __shfl_sync(0xffffffffu, base, leader);
-    return want ? base + (unsigned long long)__popc(mask & ((1u << lane) - 1u)) : ~0ull;
-}
-
-RT_DEV void wf_store_path(const WfArgs& a, uint32_t slot, const Ray& ray, V3f beta, uint32_t pixel, uint32_t depth, bool alive,
-                          const PcgRng& rng) {
-    a.ray_o[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.tm);
-    a.ray_d[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(depth | (alive ? WF_ALIVE : 0u)));
-    a.beta[slot] = make_float4(beta.x, beta.y, beta.z, __uint_as_float(pixel));
-    a.rng[slot] = make_uint2((uint32_t)rng.state, (uint32_t)(rng.state >> 32));
-}
-
-// Fill slots with fresh camera paths (frame start).
-__global__ void __launch_bounds__(256) k_wf_generate(DeviceScene sc, WfArgs a) {
-    const WfFrame f = *a.frame;
-    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;  // P is a multiple of 256
-    Ray ray;
-    ray.o = ray.d = mk3(0.0f, 0.0f, 0.0f);
-    ray.tm = 0.0f;
-    V3f beta = mk3(1.0f, 1.0f, 1.0f);
-    uint32_t pixel = 0;
-    PcgRng rng;
-    rng.state = 0;
-    bool alive = false;
-    unsigned long long k = wf_fetch(a, true);
-    if (k < f.total_paths) {
-        wf_generate(sc, f, k, ray, beta, pixel, rng);
-        alive = true;
-    }
-    wf_store_path(a, slot, ray, beta, pixel, 0u, alive, rng);
-}
-
-// Appends the slots of the lanes with `fin` set to the warp's per-class staging buffers and flushes a
-// buffer to its global queue once it holds WF_FLUSH entries.  Warp-synchronous (all 32 lanes call it).
-RT_DEV void wf_stage_append(const WfArgs& a, int buf, uint32_t (*stage)[WF_STAGE], uint32_t* cnt, bool fin, uint32_t cls,
-                            uint32_t slot, uint32_t lane) {
-    uint32_t pending = __ballot_sync(0xffffffffu, fin);
-    while (pending) {
-        const uint32_t c = __shfl_sync(0xffffffffu, cls, __ffs(pending) - 1);  // class of the lowest pending lane
-        const bool mine = fin && cls == c;
-        const uint32_t m = __ballot_sync(0xffffffffu, mine);
-        uint32_t n = cnt[c];
-        if (mine) stage[c][n + __popc(m & ((1u << lane) - 1u))] = slot;
-        n += __popc(m);
-        __syncwarp();
-        if (n >= WF_FLUSH) {
-            uint32_t base = 0;
-            if (lane == 0) base = atomicAdd(a.n_class + buf * WF_NCLASS + c, WF_FLUSH);
-            base = __shfl_sync(0xffffffffu, base, 0);
-            uint32_t* q = a.queue + (size_t)c * a.P + base;
-#pragma unroll
-            for (uint32_t k = 0; k < WF_FLUSH; k += 32u) q[k + lane] = stage[c][k + lane];
-            const uint32_t rem = n - WF_FLUSH;  // < 32
-            const uint32_t v = lane < rem ? stage[c][WF_FLUSH + lane] : 0u;
-            __syncwarp();
-            if (lane < rem) stage[c][lane] = v;
-            n = rem;
-        }
-        if (lane == 0) cnt[c] = n;
-        __syncwarp();
-        pending &= ~m;
-    }
-}
-
-template <uint32_t F, bool COUNT>
-__global__ void __launch_bounds__(WF_TRAV_THREADS) k_wf_traverse(DeviceScene sc, WfArgs a, int buf) {
-    __shared__ uint32_t s_stage[WF_TRAV_WARPS][CLS_COUNT][WF_STAGE];
-    __shared__ uint32_t s_cnt[WF_TRAV_WARPS][WF_NCLASS];
-    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    uint32_t (*stage)[WF_STAGE] = s_stage[warp];
-    uint32_t* cnt = s_cnt[warp];
-    if (lane < WF_NCLASS) cnt[lane] = 0u;
-    __syncwarp();
-    // counters of the NEXT iteration (nothing reads or writes them while this kernel runs)
-    if (blockIdx.x == 0 && threadIdx.x < WF_NCLASS) a.n_class[(buf ^ 1) * WF_NCLASS + threadIdx.x] = 0u;
-    if (blockIdx.x == 0 && threadIdx.x == WF_NCLASS) a.trav_counter[buf ^ 1] = 0u;
-    const uint32_t refill_threshold = a.frame->refill_threshold, chunk = a.frame->chunk;
-
-    uint32_t slot = WF_NO_SLOT;
-    uint32_t c_next = 0, c_end = 0;  // the warp's reserved chunk of slot indices (warp-uniform)
-    bool more = true;                // the global counter may still hold unreserved slots (warp-uniform)
-    Ray ray;
-    ray.o = ray.d = mk3(0.0f, 0.0f, 0.0f);
-    ray.tm = 0.0f;
-    RaySlab rs;
-    rs.init(ray);
-    TravState ts;
-    ts.init(0.0f);
-    ts.cur = TRAV_NONE;
-    XformCache xc;
-    xc.chain = 0;
-    xc.ro = ray;
-    PcgRng rng;
-    rng.state = 0;
-    uint2 stack[STACK_SIZE];
-    TravCounters tc;
-    uint32_t n_traced = 0;
-
-    for (;;) {
-        // ---- (1) retire the lanes whose traversal has finished --------------------------------------
-        const bool fin = slot != WF_NO_SLOT && ts.cur == TRAV_NONE;
-        if (__any_sync(0xffffffffu, fin)) {
-            uint32_t cls = 0xffu;
-            if (fin) {
-                a.hit[slot] = make_uint2(__float_as_uint(ts.best_t), ts.best_prim);
-                if (F & F_MEDIA) a.rng[slot] = make_uint2((uint32_t)rng.state, (uint32_t)(rng.state >> 32));
-                cls = ts.best_prim == 0xffffffffu ? (uint32_t)CLS_MISS : ((ts.best_kfx >> 12) & 0xfu);
-            }
-            wf_stage_append(a, buf, stage, cnt, fin, cls, slot, lane);
-            if (fin) slot = WF_NO_SLOT;
-        }
-        // ---- (2) refill idle lanes from the warp's chunk ---------------------------------------------
-        for (;;) {
-            const uint32_t wm = __ballot_sync(0xffffffffu, slot == WF_NO_SLOT);
-            if (wm == 0u) break;
-            if (c_next >= c_end) {
-                if (!more) break;
-                uint32_t base = 0;
-                if (lane == 0) base = atomicAdd(a.trav_counter + buf, chunk);
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (base >= a.P) {
-                    more = false;
-                    break;
-                }
-                c_next = base;
-                c_end = min(base + chunk, a.P);
-            }
-            const uint32_t avail = c_end - c_next;
-            const uint32_t rank = __popc(wm & ((1u << lane) - 1u));
-            const bool take = slot == WF_NO_SLOT && rank < avail;
-            const uint32_t idx = c_next + rank;
-            c_next += min((uint32_t)__popc(wm), avail);
-            if (take) {
-                const float4 rd = a.ray_d[idx];
-                if (__float_as_uint(rd.w) & WF_ALIVE) {
-                    const float4 ro = a.ray_o[idx];
-                    slot = idx;
-                    n_traced++;
-                    ray.o = mk3(ro.x, ro.y, ro.z);
-                    ray.d = mk3(rd.x, rd.y, rd.z);
-                    ray.tm = ro.w;
-                    ts.init(3.402823466e+38f);
-                    if (F & F_XFORM) {
-                        xc.chain = 0;
-                        xc.ro = ray;
-                    }
-                    if (F & F_MEDIA) {
-                        const uint2 st = a.rng[idx];
-                        rng.state = ((unsigned long long)st.y << 32) | st.x;
-                    }
-                    if (vec3a_near_one(ray.d)) {
-                        rs.init(ray);
-                    } else {
-                        // main.rs:39: a non-unit direction loses the path; it retires as a miss with zero throughput
-                        const float4 b = a.beta[idx];
-                        a.beta[idx] = make_float4(0.0f, 0.0f, 0.0f, b.w);
-                        ts.cur = TRAV_NONE;
-                    }
-                }
-            }
-        }
-        if (!__any_sync(0xffffffffu, slot != WF_NO_SLOT)) break;
-        // ---- (3) traverse until too few lanes are busy (and there are rays left to fetch) -------------
-        const bool can_refill = more || c_next < c_end;
-        for (;;) {
-            while (!(ts.cur & LEAF_FLAG) && ts.cur != TRAV_NONE) node_visit<COUNT>(sc, rs, 1e-3f, ts, stack, &tc);
-            if (ts.cur != TRAV_NONE) {
-                leaf_visit<F, COUNT>(sc, ray, 1e-3f, ts, xc, rng, false, &tc);
-                ts.pop(stack);
-            }
-            const uint32_t busy = __ballot_sync(0xffffffffu, ts.cur != TRAV_NONE);
-            if (busy == 0u) break;
-            if (can_refill && (uint32_t)__popc(busy) < refill_threshold) break;
-        }
-    }
-    // ---- flush what is left in the staging buffers ---------------------------------------------------
-    for (uint32_t c = 0; c < (uint32_t)CLS_COUNT; c++) {
-        const uint32_t n = cnt[c];
-        if (n == 0u) continue;
-        uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(a.n_class + buf * WF_NCLASS + c, n);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        for (uint32_t k = lane; k < n; k += 32u) a.queue[(size_t)c * a.P + base + k] = stage[c][k];
-    }
-    const unsigned long long traced = warp_sum_u64(n_traced);
-    if (lane == 0 && traced) {
-        atomicAdd(a.n_class + buf * WF_NCLASS + 7, (uint32_t)traced);
-        atomicAdd(a.stats + 0, traced);
-    }
-    if (COUNT) {
-        unsigned long long nv = warp_sum_u64(tc.node_visits), bt = warp_sum_u64(tc.box_tests), pt = warp_sum_u64(tc.prim_tests);
-        if (lane == 0) {
-            atomicAdd(a.stats + 2, nv);
-            atomicAdd(a.stats + 3, bt);
-            atomicAdd(a.stats + 4, pt);
-        }
-    }
-}
-
-template <uint32_t F, int CLS>
-__global__ void __launch_bounds__(WF_SHADE_THREADS) k_wf_shade(DeviceScene sc, WfArgs a, int buf) {
-    const uint32_t n = a.n_class[buf * WF_NCLASS + CLS];
-    const uint32_t n_round = (n + 31u) & ~31u;
-    if (blockIdx.x * blockDim.x >= n_round) return;
-    const WfFrame f = *a.frame;
-    const uint32_t* queue = a.queue + (size_t)CLS * a.P;
-    unsigned long long n_shade = 0;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
-        const bool active = i < n;
-        uint32_t slot = 0, pixel = 0, depth = 0;
-        Ray ray;
-        ray.o = ray.d = mk3(0.0f, 0.0f, 0.0f);
-        ray.tm = 0.0f;
-        V3f beta = mk3(0.0f, 0.0f, 0.0f);
-        PcgRng rng;
-        rng.state = 0;
-        bool alive = false;
-        if (active) {
-            slot = queue[i];
-            const float4 rd = a.ray_d[slot], bt = a.beta[slot];
-            ray.d = mk3(rd.x, rd.y, rd.z);
-            beta = mk3(bt.x, bt.y, bt.z);
-            pixel = __float_as_uint(bt.w);
-            V3f add = mk3(0.0f, 0.0f, 0.0f);
-            if (CLS == CLS_MISS) {
-                // main.rs:58; a path dropped by the unit-direction check arrives here with beta == 0
-                if (beta.x != 0.0f || beta.y != 0.0f || beta.z != 0.0f) add = beta * sky_color(sc, ray.d);
-            } else {
-                const float4 ro = a.ray_o[slot];
-                const uint2 st = a.rng[slot], ht = a.hit[slot];
-                ray.o = mk3(ro.x, ro.y, ro.z);
-                ray.tm = ro.w;
-                depth = __float_as_uint(rd.w) & 0xffu;
-                rng.state = ((unsigned long long)st.y << 32) | st.x;
-                n_shade++;
-                DevPrim hp = load_prim(sc.prims, ht.y);
-                DevMaterial m = load_mat(sc, hp.mat);
-                const bool want_uv = (CLS == CLS_CLASSIC || CLS == CLS_PBR) && (m.reserved & 1u) != 0u;
-                HitRec rec = fill_hit<F>(sc, ray, ht.y, __uint_as_float(ht.x), want_uv);
-                V3f emitted, att;
-                Ray scattered;
-                bool ok = shade_cls<CLS>(sc, m, ray, rec, rng, emitted, att, scattered, (f.max_depth & DEPTH_COS_FLAG) != 0u);
-                if (CLS == CLS_CLASSIC) add = beta * emitted;  // main.rs:47 (only Emission emits, material.rs:26-28)
-                if (ok && (f.max_depth & DEPTH_RR_FLAG)) ok = russian_roulette(att, rng);
-                if (ok) {                                      // main.rs:48-54
-                    beta = beta * att;
-                    ray = scattered;
-                    depth++;
-                    alive = depth <= (f.max_depth & DEPTH_MASK);  // main.rs:40-42
-                }
-            }
-            if (add.x != 0.0f || add.y != 0.0f || add.z != 0.0f) {
-                float* px_out = f.accum + (size_t)pixel * 3u;
-                atomicAdd(px_out + 0, add.x);
-                atomicAdd(px_out + 1, add.y);
-                atomicAdd(px_out + 2, add.z);
-            }
-        }
-        // ---- regenerate a fresh camera path in place when this one ended ---------------------------
-        const bool want = active && !alive;
-        const unsigned long long k = wf_fetch(a, want);
-        if (want && k < f.total_paths) {
-            wf_generate(sc, f, k, ray, beta, pixel, rng);
-            depth = 0;
-            alive = true;
-        }
-        if (active) wf_store_path(a, slot, ray, beta, pixel, depth, alive, rng);
-    }
-    if (CLS != CLS_MISS) {
-        n_shade = warp_sum_u64(n_shade);
-        if ((threadIdx.x & 31u) == 0 && n_shade) atomicAdd(a.stats + 1, n_shade);
-    }
-}
-
-// ------------------------------------------------------------------------------------- test kernels
-// Shade parity: replay emitted + scatter for `n` (ray, record, material) cases with injected random
-// numbers (xi_stride per case), so CUDA materials and the oracle consume identical draws.
-// rec_in per case: p[3] norm[3] tang[3] uv[2] t front_face (13 floats); out per case: emitted[3]
-// attenuation[3] scat_o[3] scat_d[3] ok consumed (14 floats).
-__global__ void k_shade_cases(DeviceScene sc, const uint32_t* __restrict__ mat_ids, const float* __restrict__ rays,
-                              const float* __restrict__ recs, const float* __restrict__ xi, uint32_t xi_stride, uint32_t n,
-                              float* __restrict__ out) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    Ray r;
-    r.o = mk3(rays[6 * i], rays[6 * i + 1], rays[6 * i + 2]);
-    r.d = mk3(rays[6 * i + 3], rays[6 * i + 4], rays[6 * i + 5]);
-    r.tm = 0.0f;
-    const float* q = recs + 13 * (size_t)i;
-    HitRec rec;
-    rec.p = mk3(q[0], q[1], q[2]);
-    rec.norm = mk3(q[3], q[4], q[5]);
-    rec.tang = mk3(q[6], q[7], q[8]);
-    rec.u = q[9];
-    rec.v = q[10];
-    rec.t = q[11];
-    rec.front_face = q[12] != 0.0f;
-    rec.mat = mat_ids[i];
-    ArrayRng rng{xi + (size_t)i * xi_stride, xi_stride, 0};
-    DevMaterial m = load_mat(sc, rec.mat);
-    V3f em, att;
-    Ray sc_ray;
-    bool ok = shade(sc, m, r, rec, rng, em, att, sc_ray);
-    float* o = out + 14 * (size_t)i;
-    o[0] = em.x; o[1] = em.y; o[2] = em.z;
-    o[3] = att.x; o[4] = att.y; o[5] = att.z;
-    o[6] = sc_ray.o.x; o[7] = sc_ray.o.y; o[8] = sc_ray.o.z;
-    o[9] = sc_ray.d.x; o[10] = sc_ray.d.y; o[11] = sc_ray.d.z;
-    o[12] = ok ? 1.0f : 0.0f;
-    o[13] = (float)rng.i;
-}
-
-// Texture / sky parity: value(uv, p) of texture `tex` (or sky(d) when tex == 0xffffffff, d = p).
-__global__ void k_texture_cases(DeviceScene sc, uint32_t tex, const float* __restrict__ uv, const float* __restrict__ p,
-                                uint32_t n, float* __restrict__ out) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    V3f pt = mk3(p[3 * i], p[3 * i + 1], p[3 * i + 2]);
-    V3f c = tex == 0xffffffffu ? sky_color(sc, pt) : texture_value(sc, tex, uv[2 * i], uv[2 * i + 1], pt);
-    out[3 * i] = c.x;
-    out[3 * i + 1] = c.y;
-    out[3 * i + 2] = c.z;
-}
-
 // ---------------------------------------------------------------------------------------- k_resolve
 // main.rs:98-105,127: c = sum / spp; c = c.powf(0.5); (c * 255.99) as u8 (saturating, NaN -> 0);
 // vertical flip so that output row 0 is the top of the picture.

@@ -118,7 +118,7 @@ RT_DEV void cta_shade_item(const DeviceScene& sc, const CtaArgs& a, const CtaPoo
     ray.tm = 0.0f;
     V3f beta = mk3(bt.x, bt.y, bt.z);
     const uint32_t pixel = __float_as_uint(bt.w);
-    uint32_t depth = __float_as_uint(rd.w) & 0xffu;
+    uint32_t depth = __float_as_uint(rd.w) & DEPTH_MASK;  // (the slot's alive flag is bit 31)
     V3f add = mk3(0.0f, 0.0f, 0.0f);
     bool alive = false;
     PcgRng rng;

@@ -374,11 +374,13 @@ struct Flat {
                 break;
             }
             case HKind::Medium: {
-                if (xf != 0 || bo) throw std::runtime_error("ConstantMedium under a transform / as a boundary is not supported");
+                // The wrappers around the medium (chain xf) wrap its boundary too (hitable.rs:404-436,486-505 over
+                // 536-579): the boundary primitives carry xf followed by their own wrappers, the medium carries xf.
+                // A medium as another medium's boundary flattens too; rt_scene_create answers RT_ERR_UNSUPPORTED.
                 uint32_t first = (uint32_t)o.prims.size();
-                walk(h->kids[0], 0, true);
+                walk(h->kids[0], xf, true);
                 uint32_t count = (uint32_t)o.prims.size() - first;
-                uint32_t id = prim(RT_PRIM_MEDIUM, h->mat, 0, false, {h->neg_inv_density});
+                uint32_t id = prim(RT_PRIM_MEDIUM, h->mat, xf, bo, {h->neg_inv_density});
                 o.prims[id].aux0 = first;
                 o.prims[id].aux1 = count;
                 break;

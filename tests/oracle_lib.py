@@ -75,6 +75,11 @@ def lib() -> C.CDLL:
         L.orc_refract.argtypes = [vp, vp, C.c_float, vp]
         L.orc_aabb_hit.argtypes = [vp, vp, vp, vp, C.c_float, C.c_float]
         L.orc_sky.argtypes = [C.c_uint32, vp, vp]
+        L.orc_scene_sky.argtypes = [vp, vp, vp]
+        L.orc_perlin_table.argtypes = [C.c_uint64, C.c_uint32, vp, C.c_uint32, vp, vp, vp]
+        L.orc_perlin_table.restype = None
+        L.orc_closest_hit_xi.argtypes = [vp, vp, vp, vp, C.c_size_t, C.c_float, C.c_float, vp]
+        L.orc_medium_cases.argtypes = [vp, C.c_uint32, vp, vp, vp, C.c_size_t, vp]
         _lib = L
     return _lib
 
@@ -150,6 +155,30 @@ class OracleScene:
         rc = lib().orc_scatter(self.h, mat_id, _p(ray_o), _p(ray_d), _p(rec13), _p(xi), xi.size, _p(out), C.byref(used))
         assert rc >= 0
         return rc, out, used.value
+
+    def sky(self, d):
+        d = np.ascontiguousarray(d, np.float32)
+        out = np.zeros(3, np.float32)
+        assert lib().orc_scene_sky(self.h, _p(d), _p(out)) == 0
+        return out
+
+    def closest_hit_xi(self, o, d, xi, t_min=1e-3, t_max=3.4028234663852886e38):
+        """world.hit with the media included, every random draw of ray i = xi[i]."""
+        o = np.ascontiguousarray(o, np.float32)
+        d = np.ascontiguousarray(d, np.float32)
+        xi = np.ascontiguousarray(xi, np.float32)
+        out = np.zeros(o.shape[0], dtype=HIT_DTYPE)
+        assert lib().orc_closest_hit_xi(self.h, _p(o), _p(d), _p(xi), o.shape[0], C.c_float(t_min), C.c_float(t_max), _p(out)) == 0
+        return out
+
+    def medium_cases(self, flat_prim, rays, tmm, xi):
+        rays = np.ascontiguousarray(rays, np.float32)
+        tmm = np.ascontiguousarray(tmm, np.float32)
+        xi = np.ascontiguousarray(xi, np.float32)
+        out = np.zeros((rays.shape[0], 11), np.float32)
+        rc = lib().orc_medium_cases(self.h, flat_prim, _p(rays), _p(tmm), _p(xi), rays.shape[0], _p(out))
+        assert rc == 0, rc
+        return out
 
     def texture_value(self, tex_id, uv, p):
         uv = np.ascontiguousarray(uv, np.float32)

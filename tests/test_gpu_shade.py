@@ -42,10 +42,10 @@ def _random_cases(rng, n):
                                         "furnace_disney_metal", "furnace_oren_nayar", "furnace_disney_sheen"])
 def test_scatter_matches_oracle(rtlib, oracle, scene_name):
     rt = rtlib
-    lib = rt.load_library()
+    lib = rt.load_test_library()
     hs = rt.HostScene(scene_name, 1.5)
     flat = hs.flat.contents
-    scene = rt.Scene(hs.flat, 0)
+    scene = rt.Scene(hs.flat, 0, lib=lib)
     ref = oracle.OracleScene.from_flat(hs.flat)
     rng = np.random.default_rng(1234)
     # every material kind present (at most 40 materials per kind)
@@ -80,10 +80,10 @@ def test_scatter_matches_oracle(rtlib, oracle, scene_name):
 @pytest.mark.parametrize("scene_name", ["sphere_scene", "textured", "pbr_ibl"])
 def test_textures_and_sky_match_oracle(rtlib, oracle, scene_name):
     rt = rtlib
-    lib = rt.load_library()
+    lib = rt.load_test_library()
     hs = rt.HostScene(scene_name, 1.5)
     flat = hs.flat.contents
-    scene = rt.Scene(hs.flat, 0)
+    scene = rt.Scene(hs.flat, 0, lib=lib)
     ref = oracle.OracleScene.from_flat(hs.flat)
     rng = np.random.default_rng(99)
     n = 2000
@@ -114,10 +114,12 @@ def test_textures_and_sky_match_oracle(rtlib, oracle, scene_name):
     out = np.zeros((n, 3), np.float32)
     rc = lib.rt_test_texture_cases(scene._h, 0xFFFFFFFF, uv.ctypes.data, dirs.ctypes.data, n, out.ctypes.data)
     assert rc == 0
-    L = oracle.lib()
-    want = np.zeros((n, 3), np.float32)
-    if flat.sky.kind != 2:
-        for i in range(n):
-            L.orc_sky(flat.sky.kind, dirs[i].ctypes.data, want[i].ctypes.data)
+    want = np.stack([ref.sky(dirs[i]) for i in range(n)])
+    if flat.sky.kind == 2:
+        # tex_sky_color (demo_scene.rs:22-26): uv through acos/atan2 (libm vs libdevice ulps) selects a TEXEL, so a
+        # direction within an ulp of a texel edge may pick the neighbour: exact on all but a handful of directions
+        same = np.all(out.view(np.uint32) == want.view(np.uint32), axis=1)
+        assert (~same).sum() <= 4, f"env-map sky: {(~same).sum()} of {n} directions differ"
+    else:
         np.testing.assert_allclose(out, want, rtol=1e-6, atol=1e-7)
     scene.close()

@@ -12,13 +12,46 @@ SCENES = ["test_sphere", "sphere_scene", "textured", "cover_defocus", "cover_4k_
           "cornell_box", "cornell_box_solid", "final_scene", "pbr_ibl", "furnace_diffuse", "furnace_disney_metal"]
 
 
-def test_library_exports_every_header_symbol(rtlib):
+def _dynamic_symbols(path):
+    """Defined symbols of the shared object's dynamic symbol table (`nm -D --defined-only`)."""
+    import subprocess
+    out = subprocess.check_output(["nm", "-D", "--defined-only", path], text=True)
+    return {ln.split()[-1] for ln in out.splitlines() if ln.strip()}
+
+
+def test_library_exports_exactly_the_header(rtlib):
+    """librtgpu.so's dynamic symbol table == the functions include/rtgpu.h declares: nothing missing, no rt_test_*
+    hook, no C++ internal (csrc/exports.map).  The ctypes mirror's list is pinned to the same set."""
     lib = rtlib.load_library()
     header = open(os.path.join(os.path.dirname(rtlib.api.HERE), "include", "rtgpu.h")).read()
     declared = set(re.findall(r"\b(rt_[a-z0-9_]+)\s*\(", header))
+    exported = _dynamic_symbols(rtlib.LIB_PATH)
+    assert exported == declared, exported ^ declared
     assert declared == set(rtlib.EXPORTED_SYMBOLS), declared ^ set(rtlib.EXPORTED_SYMBOLS)
     for sym in declared:
         assert getattr(lib, sym) is not None
+    # the test library = the same ABI plus the hooks, nothing else
+    extra = _dynamic_symbols(rtlib.api.TEST_LIB_PATH) - declared
+    assert extra == {"rt_test_shade_cases", "rt_test_texture_cases", "rt_test_medium_cases", "rt_test_closest_hit_xi",
+                     "rt_test_bvh_validate"}, extra
+
+
+def test_library_reads_no_environment(rtlib):
+    """The shipped library never looks at the environment: the one getenv in csrc/ sits inside dev_knob() behind
+    #ifdef RT_DEV_KNOBS (tools/build_variant.py builds), and the product build does not define it."""
+    csrc = os.path.join(rtlib.api.HERE, "csrc")
+    hits = []
+    for f in sorted(os.listdir(csrc)):
+        if f.endswith((".cu", ".cuh", ".cpp", ".hpp", ".h")):
+            for n, line in enumerate(open(os.path.join(csrc, f), errors="replace"), 1):
+                if "getenv" in line and not line.lstrip().startswith("//"):
+                    hits.append((f, n, line.strip()))
+    assert len(hits) == 1 and hits[0][0] == "rtgpu.cu", hits
+    src = open(os.path.join(csrc, "rtgpu.cu")).read()
+    i = src.index("getenv(")
+    assert "#ifdef RT_DEV_KNOBS" in src[max(0, i - 200):i]
+    from ray_tracing_in_one_weekend_b200 import build
+    assert not any("RT_DEV_KNOBS" in f for f in build.NVCC_FLAGS + build.HOST_FLAGS)
 
 
 def test_struct_layouts_match_header(rtlib):
@@ -56,10 +89,9 @@ def test_cover_100k_motion_scene_shape(rtlib):
 @pytest.mark.parametrize("name", ["test_sphere", "sphere_scene", "cornell_box", "final_scene", "cover_4k_motion", "pbr_ibl"])
 @pytest.mark.parametrize("leaf_max", [1, 4, 8])
 def test_bvh_invariants(rtlib, name, leaf_max):
-    lib = rtlib.load_library()
+    lib = rtlib.load_test_library()
     hs = rtlib.HostScene(name, 1.5)
     info = rtlib.api.RtBvhInfo()
-    lib.rt_test_bvh_validate.argtypes = [C.POINTER(rtlib.RtFlatScene), C.c_uint32, C.POINTER(rtlib.api.RtBvhInfo)]
     rc = lib.rt_test_bvh_validate(hs.flat, leaf_max, C.byref(info))
     assert rc == 0, lib.rt_last_error()
     assert info.node_bytes == 128 and info.max_leaf_prims <= leaf_max and info.n_nodes >= 1
@@ -230,7 +262,7 @@ def _synthetic_flat(api, mats, prim_mats, radii):
         p[i].kind, p[i].mat = 0, mi  # RT_PRIM_SPHERE
         p[i].g[0], p[i].g[1], p[i].g[2], p[i].g[3] = float(i), 0.0, 0.0, r
     f = api.RtFlatScene()
-    f.abi_version = 1
+    f.abi_version = api.RT_ABI_VERSION
     f.n_prims, f.n_materials, f.n_textures = len(prim_mats), len(mats), 1
     f.prims, f.materials, f.textures = p, m, tex
     return f, (tex, m, p)
