@@ -237,8 +237,14 @@ typedef struct RtBvhInfo {
     uint32_t node_bytes;
     uint32_t builder;     /* 0 = host SAH, 1 = GPU LBVH */
     float build_ms;       /* wall clock of the build inside rt_scene_create */
+    uint64_t upload_bytes; /* size of the ONE host-to-device copy that carried every table of the scene */
 } RtBvhInfo;
 int rt_scene_bvh_info(const RtScene* scene, RtBvhInfo* out);
+
+/* CUDA-event durations (ms) of the render kernels of the last n <= min(capacity, 32) rt_render_device /
+ * rt_render_reduce* calls on this scene, oldest first — measured on the stream each kernel ran on; waits for those
+ * kernels to finish.  Lets a caller time the kernel of an asynchronous frame loop without a synchronisation per frame. */
+int rt_scene_kernel_times(RtScene* scene, double* out_ms, int capacity, int* out_n);
 
 /* The checks rt_scene_create runs on a description, without a device: RT_OK, RT_ERR_ARG or RT_ERR_UNSUPPORTED. */
 int rt_flat_validate(const RtFlatScene* desc);

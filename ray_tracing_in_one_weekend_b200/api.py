@@ -98,7 +98,7 @@ class RtFlatScene(C.Structure):
 class RtBvhInfo(C.Structure):
     _fields_ = [("n_nodes", C.c_uint32), ("n_world_prims", C.c_uint32), ("max_depth", C.c_uint32),
                 ("max_leaf_prims", C.c_uint32), ("sah_cost", C.c_float), ("node_bytes", C.c_uint32),
-                ("builder", C.c_uint32), ("build_ms", C.c_float)]
+                ("builder", C.c_uint32), ("build_ms", C.c_float), ("upload_bytes", C.c_uint64)]
 
 
 class RtHit(C.Structure):
@@ -134,6 +134,7 @@ EXPORTED_SYMBOLS = [
     "rt_flat_shade_queues", "rt_last_error", "rt_host_scene_build", "rt_host_scene_flat", "rt_host_scene_destroy",
     "rt_flat_validate", "rt_release_cached_memory", "rt_partition_samples", "rt_comm_unique_id", "rt_comm_create",
     "rt_comm_create_all", "rt_comm_info", "rt_comm_destroy", "rt_render_reduce", "rt_render_reduce_device",
+    "rt_scene_kernel_times",
 ]
 
 _lib: Optional[C.CDLL] = None
@@ -148,6 +149,7 @@ def _declare(lib: C.CDLL) -> None:
     lib.rt_scene_destroy.argtypes = [vp]
     lib.rt_scene_destroy.restype = None
     lib.rt_scene_bvh_info.argtypes = [vp, C.POINTER(RtBvhInfo)]
+    lib.rt_scene_kernel_times.argtypes = [vp, C.POINTER(C.c_double), C.c_int, C.POINTER(C.c_int)]
     lib.rt_flat_shade_queues.argtypes = [vp, C.POINTER(C.c_uint8), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
     lib.rt_flat_validate.argtypes = [C.POINTER(RtFlatScene)]
     lib.rt_release_cached_memory.argtypes = []
@@ -346,6 +348,13 @@ class Scene:
         info = RtBvhInfo()
         _check(self._lib.rt_scene_bvh_info(self._h, C.byref(info)), self._lib)
         return info
+
+    def kernel_times(self, n: int = 32):
+        """CUDA-event durations (ms) of the last n <= 32 render kernels on this scene, oldest first (waits for them)."""
+        buf = (C.c_double * max(n, 1))()
+        got = C.c_int()
+        _check(self._lib.rt_scene_kernel_times(self._h, buf, n, C.byref(got)), self._lib)
+        return [buf[i] for i in range(got.value)]
 
     def closest_hit(self, o: np.ndarray, d: np.ndarray, t_min: float = 1e-3, t_max: float = 3.4028234663852886e38,
                     times: Optional[np.ndarray] = None) -> np.ndarray:

@@ -51,31 +51,38 @@ def _run(cmd: list[str]) -> str:
     return r.stdout + r.stderr
 
 
-def build_all(force: bool = False, verbose: bool = False) -> str:
+def build_all(force: bool = False, verbose: bool = False, extra: tuple = (), out_dir: str | None = None) -> str:
+    """Builds librtgpu.so (+ librtgpu_test.so).  `extra` nvcc flags and `out_dir` are for development variants
+    (tools/build_variant.py): objects and libraries then go to `out_dir` instead of the package directory."""
     hdrs = [os.path.join(CSRC, h) for h in HEADERS]
+    obj_dir = out_dir or CSRC
+    lib_dir = out_dir or HERE
+    os.makedirs(obj_dir, exist_ok=True)
+    lib, test_lib = os.path.join(lib_dir, "librtgpu.so"), os.path.join(lib_dir, "librtgpu_test.so")
+    nvcc_flags = NVCC_FLAGS + list(extra)
     objs = []
     log = []
     for src in HOST_SRCS:
-        obj = os.path.join(CSRC, src.replace(".cpp", ".o"))
+        obj = os.path.join(obj_dir, src.replace(".cpp", ".o"))
         if force or _stale(obj, [os.path.join(CSRC, src)] + hdrs):
             log.append(_run([CXX] + HOST_FLAGS + ["-c", src, "-o", obj]))
         objs.append(obj)
     jobs = []
     test_objs = []
     for src in CUDA_SRCS + TEST_SRCS:
-        obj = os.path.join(CSRC, src.replace(".cu", ".o"))
+        obj = os.path.join(obj_dir, src.replace(".cu", ".o"))
         if force or _stale(obj, [os.path.join(CSRC, src)] + hdrs):
-            jobs.append([NVCC] + NVCC_FLAGS + ["-c", src, "-o", obj])
+            jobs.append([NVCC] + nvcc_flags + ["-c", src, "-o", obj])
         (test_objs if src in TEST_SRCS else objs).append(obj)
     for f in CTA_FEATURE_SETS:
-        obj = os.path.join(CSRC, f"cta_f{f}.o")
+        obj = os.path.join(obj_dir, f"cta_f{f}.o")
         if force or _stale(obj, [os.path.join(CSRC, "cta_inst.cu")] + hdrs):
-            jobs.append([NVCC] + NVCC_FLAGS + [f"-DRT_CTA_F={f}", "-c", "cta_inst.cu", "-o", obj])
+            jobs.append([NVCC] + nvcc_flags + [f"-DRT_CTA_F={f}", "-c", "cta_inst.cu", "-o", obj])
         objs.append(obj)
     for f in CTA_NO_PBR_SETS:
-        obj = os.path.join(CSRC, f"cta_f{f}_m3f.o")
+        obj = os.path.join(obj_dir, f"cta_f{f}_m3f.o")
         if force or _stale(obj, [os.path.join(CSRC, "cta_inst.cu")] + hdrs):
-            jobs.append([NVCC] + NVCC_FLAGS + [f"-DRT_CTA_F={f}", "-DRT_CTA_CLS_MASK=0x3f", "-DRT_CTA_SUFFIX=_m3f", "-c", "cta_inst.cu", "-o", obj])
+            jobs.append([NVCC] + nvcc_flags + [f"-DRT_CTA_F={f}", "-DRT_CTA_CLS_MASK=0x3f", "-DRT_CTA_SUFFIX=_m3f", "-c", "cta_inst.cu", "-o", obj])
         objs.append(obj)
     if jobs:  # the CUDA units are independent: compile them side by side
         from concurrent.futures import ThreadPoolExecutor
@@ -83,14 +90,14 @@ def build_all(force: bool = False, verbose: bool = False) -> str:
             log.extend(ex.map(_run, jobs))
     # exports.map: the dynamic symbol table holds the rt_* entry points and nothing else (no C++ internals)
     link = ["-gencode", "arch=compute_100a,code=sm_100a", "-lz", "-lnccl", "-Xlinker", "--version-script=" + os.path.join(CSRC, "exports.map")]
-    if force or _stale(LIB, objs + [os.path.join(CSRC, "exports.map")]):
-        log.append(_run([NVCC, "-shared", "-o", LIB] + objs + link))
-    if force or _stale(TEST_LIB, objs + test_objs + [os.path.join(CSRC, "exports.map")]):
-        log.append(_run([NVCC, "-shared", "-o", TEST_LIB] + objs + test_objs + link))
+    if force or _stale(lib, objs + [os.path.join(CSRC, "exports.map")]):
+        log.append(_run([NVCC, "-shared", "-o", lib] + objs + link))
+    if force or _stale(test_lib, objs + test_objs + [os.path.join(CSRC, "exports.map")]):
+        log.append(_run([NVCC, "-shared", "-o", test_lib] + objs + test_objs + link))
     out = "".join(log)
     if verbose and out:
         print(out)
-    return LIB
+    return lib
 
 
 if __name__ == "__main__":

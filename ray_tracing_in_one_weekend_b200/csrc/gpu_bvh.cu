@@ -301,9 +301,16 @@ bool gpu_build_bvh4(const RtFlatScene& fs, cudaStream_t st, GpuBvhResult& out, s
     LB_TRY(cudaMemcpyAsync(d_phi, phi.data(), n * sizeof(float4), cudaMemcpyHostToDevice, st));
     LB_TRY(cudaMemsetAsync(d_flags, 0, n * sizeof(int), st));
 
-    cudaEvent_t e0, e1;
-    LB_TRY(cudaEventCreate(&e0));
-    LB_TRY(cudaEventCreate(&e1));
+    struct Events {  // destroyed on every exit path
+        cudaEvent_t a = nullptr, b = nullptr;
+        ~Events() {
+            if (a) cudaEventDestroy(a);
+            if (b) cudaEventDestroy(b);
+        }
+    } evs;
+    LB_TRY(cudaEventCreate(&evs.a));
+    LB_TRY(cudaEventCreate(&evs.b));
+    const cudaEvent_t e0 = evs.a, e1 = evs.b;
     LB_TRY(cudaEventRecord(e0, st));
     const int T = 256;
     const unsigned G = (n + T - 1) / T;
@@ -311,13 +318,16 @@ bool gpu_build_bvh4(const RtFlatScene& fs, cudaStream_t st, GpuBvhResult& out, s
     auto inv = [](float a, float b) { return b > a ? 1.0f / (b - a) : 0.0f; };
     float3 ie = make_float3(inv(clo[0], chi[0]), inv(clo[1], chi[1]), inv(clo[2], chi[2]));
     k_lbvh_morton<<<G, T, 0, st>>>(n, d_rlo, d_rhi, lo, ie, d_k0, d_v0);
+    LB_TRY(cudaGetLastError());
     size_t tmp_bytes = 0;
     LB_TRY(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, d_k0, d_k1, d_v0, d_v1, (int)n, 0, 63, st));
     unsigned char* d_tmp;
     LB_TRY(buf.alloc(&d_tmp, tmp_bytes));
     LB_TRY(cub::DeviceRadixSort::SortPairs(d_tmp, tmp_bytes, d_k0, d_k1, d_v0, d_v1, (int)n, 0, 63, st));
     k_lbvh_tree<<<G, T, 0, st>>>((int)n, d_k1, d_left, d_right, d_parent);
+    LB_TRY(cudaGetLastError());
     k_lbvh_fit<<<G, T, 0, st>>>((int)n, d_v1, d_plo, d_phi, d_left, d_right, d_parent, d_nlo, d_nhi, d_flags);
+    LB_TRY(cudaGetLastError());
     // collapse, one launch per BVH4 level (the queue length comes back to the host each level)
     uint32_t h_cnt[4] = {1u, 1u, 0u, 0u};
     const uint2 root_entry = make_uint2(0u, 0u);
@@ -336,6 +346,7 @@ bool gpu_build_bvh4(const RtFlatScene& fs, cudaStream_t st, GpuBvhResult& out, s
         LB_TRY(cudaMemsetAsync(d_cnt + nxt, 0, sizeof(uint32_t), st));
         k_lbvh_collapse<<<(count + T - 1) / T, T, 0, st>>>((int)n, count, qa, d_left, d_right, d_nlo, d_nhi, d_nodes, d_cnt, qb,
                                                          d_cnt + nxt);
+        LB_TRY(cudaGetLastError());
         LB_TRY(cudaMemcpyAsync(h_cnt, d_cnt, sizeof(h_cnt), cudaMemcpyDeviceToHost, st));
         LB_TRY(cudaStreamSynchronize(st));
         count = h_cnt[nxt];
@@ -349,8 +360,6 @@ bool gpu_build_bvh4(const RtFlatScene& fs, cudaStream_t st, GpuBvhResult& out, s
     LB_TRY(cudaGetLastError());
     float ms = 0.0f;
     LB_TRY(cudaEventElapsedTime(&ms, e0, e1));
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
     for (uint32_t p = 0; p < n; p++) out.leaf_order[p] = world[sorted[p]];
     out.nodes = d_nodes;
     out.n_nodes = h_cnt[0];

@@ -113,7 +113,12 @@ struct RtScene {
     RtCamera camera{};
     // render scratch (inside the arena): [0..15] statistics, [16] path counter of the CTA kernel, [17] megakernel work counter
     unsigned long long* scratch = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;            // around the render kernel of the last rt_render_device call
+    // Event pairs around the render kernels of the last KERNEL_RING rt_render_device calls (ev0/ev1 = the current
+    // pair): rt_scene_kernel_times reads them back without having forced a synchronisation per frame.
+    static constexpr int KERNEL_RING = 32;
+    cudaEvent_t ring[2 * KERNEL_RING] = {};
+    unsigned long long n_renders = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaEvent_t ev_last = nullptr;                       // behind the last piece of work any entry point enqueued
     cudaEvent_t ev_stage[2] = {nullptr, nullptr};        // staging pipeline of d2h_frame
     int sm_count = 0;

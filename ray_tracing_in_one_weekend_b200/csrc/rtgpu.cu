@@ -122,7 +122,9 @@ RtScene::~RtScene() {
     if (stream) cudaStreamSynchronize(stream);
     for (auto t : texobjs) cudaDestroyTextureObject(t);
     if (gpu_nodes) cudaFree(gpu_nodes);
-    for (cudaEvent_t e : {ev0, ev1, ev_last, ev_stage[0], ev_stage[1]})
+    for (cudaEvent_t e : ring)
+        if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : {ev_last, ev_stage[0], ev_stage[1]})
         if (e) cudaEventDestroy(e);
     if (stream) cudaStreamDestroy(stream);
 }
@@ -444,8 +446,9 @@ int rt_scene_create_ex(const RtFlatScene* desc, int device, uint32_t flags, RtSc
     std::unique_ptr<RtScene> s(new RtScene());
     s->device = device;
     CU_TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
-    CU_TRY(cudaEventCreate(&s->ev0));
-    CU_TRY(cudaEventCreate(&s->ev1));
+    for (cudaEvent_t& e : s->ring) CU_TRY(cudaEventCreate(&e));
+    s->ev0 = s->ring[0];
+    s->ev1 = s->ring[1];
     CU_TRY(cudaEventCreateWithFlags(&s->ev_last, cudaEventDisableTiming));
     CU_TRY(cudaEventCreateWithFlags(&s->ev_stage[0], cudaEventDisableTiming));
     CU_TRY(cudaEventCreateWithFlags(&s->ev_stage[1], cudaEventDisableTiming));
@@ -688,7 +691,8 @@ int rt_scene_create_ex(const RtFlatScene* desc, int device, uint32_t flags, RtSc
         if (p.kind == RT_PRIM_XYRECT || p.kind == RT_PRIM_XZRECT || p.kind == RT_PRIM_YZRECT) s->features |= F_RECT;
     }
     s->camera = c;
-    s->bvh = RtBvhInfo{(uint32_t)bvh.nodes.size(), bvh.n_world_prims, bvh.max_depth, bvh.max_leaf_prims, bvh.sah_cost, (uint32_t)sizeof(BvhNode4), builder, build_ms};
+    s->bvh = RtBvhInfo{(uint32_t)bvh.nodes.size(), bvh.n_world_prims, bvh.max_depth, bvh.max_leaf_prims, bvh.sah_cost, (uint32_t)sizeof(BvhNode4), builder, build_ms,
+                       (uint64_t)total};
     CU_TRY(cudaStreamSynchronize(s->stream));  // the staging buffer goes back to the cache when this function returns
     stage("upload + sync");
     *out = s.release();
@@ -719,6 +723,22 @@ int rt_flat_validate(const RtFlatScene* desc) {
 int rt_scene_bvh_info(const RtScene* scene, RtBvhInfo* out) {
     if (!scene || !out) return fail(RT_ERR_ARG, "NULL argument");
     *out = scene->bvh;
+    return RT_OK;
+}
+
+int rt_scene_kernel_times(RtScene* s, double* out_ms, int capacity, int* out_n) {
+    if (!s || !out_ms || !out_n || capacity < 0) return fail(RT_ERR_ARG, "bad argument");
+    CU_TRY(cudaSetDevice(s->device));
+    const unsigned long long have = std::min<unsigned long long>(s->n_renders, (unsigned long long)RtScene::KERNEL_RING);
+    const int n = (int)std::min<unsigned long long>(have, (unsigned long long)capacity);
+    for (int k = 0; k < n; k++) {  // oldest of the last n first
+        const int slot = (int)((s->n_renders - (unsigned long long)n + (unsigned long long)k) % RtScene::KERNEL_RING);
+        float ms = 0.0f;
+        CU_TRY(cudaEventSynchronize(s->ring[2 * slot + 1]));
+        CU_TRY(cudaEventElapsedTime(&ms, s->ring[2 * slot], s->ring[2 * slot + 1]));
+        out_ms[k] = ms;
+    }
+    *out_n = n;
     return RT_OK;
 }
 
@@ -825,6 +845,9 @@ int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* c
     uint32_t launches = 0;
     if (n_samples) {
         CU_TRY(cudaMemsetAsync(s->scratch, 0, 18 * sizeof(unsigned long long), st));  // statistics + both work counters
+        const int slot = (int)(s->n_renders++ % RtScene::KERNEL_RING);
+        s->ev0 = s->ring[2 * slot];
+        s->ev1 = s->ring[2 * slot + 1];
         CU_TRY(cudaEventRecord(s->ev0, st));
         if (mode == RT_MODE_CTA_WAVEFRONT) {
             const CtaPlan* plan = nullptr;

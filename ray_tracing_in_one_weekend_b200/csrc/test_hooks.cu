@@ -281,7 +281,7 @@ RT_TEST_API int rt_test_bvh_validate(const RtFlatScene* desc, uint32_t leaf_max,
         int want = (desc->prims[i].flags & RT_PRIM_FLAG_BOUNDARY_ONLY) ? 0 : 1;
         if (seen[i] != want) return fail(RT_ERR_ARG, "bvh: primitive referenced " + std::to_string(seen[i]) + " times");
     }
-    if (info) *info = RtBvhInfo{(uint32_t)bvh.nodes.size(), bvh.n_world_prims, bvh.max_depth, bvh.max_leaf_prims, bvh.sah_cost, (uint32_t)sizeof(BvhNode4), 0u, 0.0f};
+    if (info) *info = RtBvhInfo{(uint32_t)bvh.nodes.size(), bvh.n_world_prims, bvh.max_depth, bvh.max_leaf_prims, bvh.sah_cost, (uint32_t)sizeof(BvhNode4), 0u, 0.0f, 0ull};
     return RT_OK;
 }
 

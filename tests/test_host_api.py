@@ -9,7 +9,8 @@ import numpy as np
 import pytest
 
 SCENES = ["test_sphere", "sphere_scene", "textured", "cover_defocus", "cover_4k_motion", "simple_light_scene",
-          "cornell_box", "cornell_box_solid", "final_scene", "pbr_ibl", "furnace_diffuse", "furnace_disney_metal"]
+          "cornell_box", "cornell_box_solid", "final_scene", "pbr_ibl", "furnace_diffuse", "furnace_disney_metal",
+          "smoke_instances"]
 
 
 def _dynamic_symbols(path):
@@ -297,3 +298,95 @@ def test_shade_queues_synthetic_edge_cases(rtlib):
     f2, keep2 = _synthetic_flat(api, [1], [5], [1.0])
     assert lib.rt_flat_shade_queues(C.byref(f2), mq if False else (C.c_uint8 * 1)(), C.byref(qc), C.byref(qo)) < 0
     assert b"material" in lib.rt_last_error()
+
+
+# ------------------------------------------------------------------------------------------- ABI 2 additions
+@pytest.mark.parametrize("name,needle", [("unsupported_nested_medium", b"boundary of a ConstantMedium"),
+                                         ("unsupported_disney_metal_rect", b"stale HitRecord.tang"),
+                                         ("unsupported_image_isotropic_medium", b"stale HitRecord.uv")])
+def test_unreproducible_scenes_are_refused(rtlib, name, needle):
+    """Quirk A4 and stochastic boundaries: the flattener accepts what the reference's API accepts,
+    rt_flat_validate / rt_scene_create answer RT_ERR_UNSUPPORTED with the reason instead of rendering a picture the
+    reference would not produce."""
+    lib = rtlib.load_library()
+    hs = rtlib.HostScene(name, 1.5)
+    assert lib.rt_flat_validate(hs.flat) == rtlib.RT_ERR_UNSUPPORTED
+    assert needle in lib.rt_last_error()
+    out = C.c_void_p()
+    assert lib.rt_scene_create(hs.flat, 0, C.byref(out)) == rtlib.RT_ERR_UNSUPPORTED  # checked before any device call
+    assert not out.value
+
+
+def test_media_under_wrappers_flatten_with_prefixed_chains(rtlib):
+    """smoke_instances: Translate(ConstantMedium(Sphere)), Translate(RotateY(ConstantMedium(GBox))),
+    RotateY(ConstantMedium(Translate(GBox))) — the medium record carries the wrappers AROUND it, every boundary
+    primitive's chain starts with exactly those ops, and the description validates."""
+    hs = rtlib.HostScene("smoke_instances", 1.0)
+    f = hs.flat.contents
+    rtlib.flat_validate(hs.flat)
+    media = [f.prims[i] for i in range(f.n_prims) if f.prims[i].kind == 5]
+    assert len(media) == 3 and all(m.xform != 0 for m in media)
+    depth = []
+    for m in media:
+        mc = f.xform_chains[m.xform]
+        for k in range(m.aux1):
+            b = f.prims[m.aux0 + k]
+            assert b.flags & 1
+            bc = f.xform_chains[b.xform]
+            assert bc.n_ops >= mc.n_ops
+            for j in range(mc.n_ops):
+                x, y = f.xform_ops[bc.first_op + j], f.xform_ops[mc.first_op + j]
+                assert (x.kind, list(x.v)) == (y.kind, list(y.v))
+        depth.append((mc.n_ops, f.xform_chains[f.prims[m.aux0].xform].n_ops))
+    assert sorted(depth) == [(1, 1), (1, 2), (2, 2)]
+    # a boundary chain that does not start with the medium's chain is a malformed description
+    bad = rtlib.RtFlatScene.from_buffer_copy(bytes(f))
+    prims = (rtlib.api.RtPrim * f.n_prims)()
+    C.memmove(prims, f.prims, C.sizeof(prims))
+    mi = [i for i in range(f.n_prims) if prims[i].kind == 5][0]
+    prims[prims[mi].aux0].xform = 0
+    bad.prims = prims
+    lib = rtlib.load_library()
+    assert lib.rt_flat_validate(C.byref(bad)) == rtlib.RT_ERR_ARG and b"chain" in lib.rt_last_error()
+
+
+def test_partition_samples_matches_the_reference_arithmetic(rtlib):
+    lib = rtlib.load_library()
+    b, e = C.c_uint32(), C.c_uint32()
+    for begin, end, n in [(0, 256, 8), (0, 37, 2), (5, 5, 3), (3, 10, 4), (0, 1, 8), (100, 4196, 8)]:
+        spans = []
+        for r in range(n):
+            assert lib.rt_partition_samples(begin, end, n, r, C.byref(b), C.byref(e)) == 0
+            spans.append((b.value, e.value))
+        assert spans[0][0] == begin and spans[-1][1] == end
+        assert all(spans[k][1] == spans[k + 1][0] for k in range(n - 1))
+        sizes = [y - x for x, y in spans]
+        assert max(sizes) - min(sizes) <= 1 and sizes == sorted(sizes, reverse=True)
+    assert lib.rt_partition_samples(0, 8, 0, 0, C.byref(b), C.byref(e)) == -1
+    assert lib.rt_partition_samples(0, 8, 2, 2, C.byref(b), C.byref(e)) == -1
+    assert lib.rt_partition_samples(9, 8, 2, 0, C.byref(b), C.byref(e)) == -1
+
+
+def test_comm_errors_are_codes(rtlib):
+    """The multi-GPU entry points fail with codes, never abort: bad arguments -> RT_ERR_ARG; without a CUDA device
+    -> RT_ERR_CUDA (no CPU fallback for the reduce either)."""
+    import torch
+    lib = rtlib.load_library()
+    out = C.c_void_p()
+    assert lib.rt_comm_create(None, 2, 0, 0, C.byref(out)) == -1
+    uid = (C.c_uint8 * 128)()
+    assert lib.rt_comm_create(uid, 2, 2, 0, C.byref(out)) == -1
+    assert lib.rt_comm_create(uid, 0, 0, 0, C.byref(out)) == -1
+    assert lib.rt_comm_create_all(None, 1, C.byref(out)) == -1
+    devs = (C.c_int * 2)(0, 0)
+    assert lib.rt_comm_create_all(devs, 0, C.byref(out)) == -1
+    assert lib.rt_render_reduce(None, None, None, None, None) == -1
+    assert lib.rt_render_reduce_device(None, None, None, None, None) == -1
+    assert lib.rt_comm_info(None, None, None, None) == -1
+    lib.rt_comm_destroy(None)
+    lib.rt_release_cached_memory()
+    if not torch.cuda.is_available():
+        one = (C.c_int * 1)(0)
+        assert lib.rt_comm_create_all(one, 1, C.byref(out)) == rtlib.RT_ERR_CUDA
+        assert lib.rt_comm_create(uid, 1, 0, 0, C.byref(out)) == rtlib.RT_ERR_CUDA
+        assert not out.value

@@ -197,3 +197,119 @@ def test_reference_bvh_node_counts(oracle):
     assert kinds.count(5) == 2
     sc = oracle.OracleScene.builtin("final_scene", 1.0)
     assert sc.flat.contents.n_prims == 1 + 1000 + 5 + 400 * 6 + 1 + 1 + 1
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# K13-K15: known-answer vectors for the rand 0.8.5 pieces SURVEY App. B restates from memory — UniformInt's zone
+# rejection (`gen_range(0..3)`, hitable.rs:183), `SliceRandom::shuffle` (texture.rs:72,76,80) — and for the Perlin
+# table construction order (texture.rs:62-82).  The literals below were derived with the INDEPENDENT pure-Python
+# restatement of that specification kept in this file (`_PyXoshiro`), from the K12-pinned xoshiro256++ stream
+# seeded with SplitMix64(1995); they pin the oracle (C++), the product's host RNG (C++) and the Python restatement
+# to one another and to the written specification.  (They cannot pin the specification to the crate itself: no Rust
+# toolchain / crate source here — "parity unpinned" stands for that last step.)
+class _PyXoshiro:
+    M = (1 << 64) - 1
+
+    def __init__(self, seed):
+        self.s = []
+        state = seed
+        for _ in range(4):  # SplitMix64 (App. B seed_from_u64)
+            state = (state + 0x9E3779B97F4A7C15) & self.M
+            z = state
+            z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & self.M
+            z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & self.M
+            self.s.append(z ^ (z >> 31))
+
+    @staticmethod
+    def _rotl(x, k):
+        return ((x << k) | (x >> (64 - k))) & _PyXoshiro.M
+
+    def next_u64(self):
+        s = self.s
+        r = (self._rotl((s[0] + s[3]) & self.M, 23) + s[0]) & self.M
+        t = (s[1] << 17) & self.M
+        s[2] ^= s[0]
+        s[3] ^= s[1]
+        s[1] ^= s[2]
+        s[0] ^= s[3]
+        s[2] ^= t
+        s[3] = self._rotl(s[3], 45)
+        return r
+
+    def next_u32(self):
+        return self.next_u64() >> 32
+
+    def gen_f32(self):
+        return np.float32(self.next_u32() >> 8) * np.float32(2.0 ** -24)
+
+    def below_u64(self, rng):  # UniformInt<usize>::sample_single
+        zone = ((rng << (64 - rng.bit_length())) & self.M) - 1
+        while True:
+            m = self.next_u64() * rng
+            if (m & self.M) <= zone:
+                return m >> 64
+
+    def below_u32(self, rng):  # gen_index -> UniformInt<u32>::sample_single
+        zone = ((rng << (32 - rng.bit_length())) & 0xFFFFFFFF) - 1
+        while True:
+            m = self.next_u32() * rng
+            if (m & 0xFFFFFFFF) <= zone:
+                return m >> 32
+
+
+K13_GEN_RANGE_3 = [2, 0, 1, 1, 0, 1, 0, 1, 1, 2, 2, 1, 1, 2, 2, 1]          # seed 1995, gen_range(0..3) x 16
+K14_SHUFFLE_10 = [9, 8, 5, 4, 6, 2, 1, 7, 3, 0]                              # seed 1995, (0..10).shuffle()
+K15_RAND_VEC = [[0x3F740566, 0x3F16BF0A, 0xBED31424], [0x3EA90238, 0xBF64C7C0, 0xBE130BC8], [0x3DA4FD90, 0xBF539CAA, 0xBE9A34C0]]
+K15_PERM_X = [201, 114, 245, 225, 76, 60, 50, 128]
+K15_PERM_Y = [20, 101, 92, 233, 255, 183, 238, 139]
+K15_PERM_Z = [188, 220, 71, 59, 219, 92, 202, 124]
+
+
+def test_k13_gen_range_known_answer(oracle):
+    L = oracle.lib()
+    out = (C.c_uint64 * 16)()
+    L.orc_gen_range(C.c_uint64(1995), C.c_uint64(3), 16, out)
+    assert list(out) == K13_GEN_RANGE_3
+    r = _PyXoshiro(1995)
+    assert [r.below_u64(3) for _ in range(16)] == K13_GEN_RANGE_3
+
+
+def test_k14_shuffle_known_answer(oracle):
+    L = oracle.lib()
+    out = (C.c_uint32 * 10)()
+    L.orc_shuffle(C.c_uint64(1995), 10, out)
+    assert list(out) == K14_SHUFFLE_10
+    r, p = _PyXoshiro(1995), list(range(10))
+    for i in range(9, 0, -1):
+        j = r.below_u32(i + 1)
+        p[i], p[j] = p[j], p[i]
+    assert p == K14_SHUFFLE_10
+
+
+def test_k15_perlin_table_known_answer(oracle, rtlib):
+    """texture.rs:62-82: 256 x (x, y, z) draws in [-1,1), then three shuffles that CONTINUE on the same index vector.
+    Oracle (orc_perlin_table), product host API (Perlin table 0 of sphere_scene = the first consumer of the main
+    thread's RNG, seed 1995, demo_scene.rs:41) and the Python restatement agree with the literals."""
+    L = oracle.lib()
+    vec = np.zeros((3, 3), np.float32)
+    px, py, pz = ((C.c_uint32 * 8)() for _ in range(3))
+    L.orc_perlin_table(C.c_uint64(1995), 3, vec.ctypes.data, 8, px, py, pz)
+    assert vec.view(np.uint32).tolist() == K15_RAND_VEC
+    assert (list(px), list(py), list(pz)) == (K15_PERM_X, K15_PERM_Y, K15_PERM_Z)
+    hs = rtlib.HostScene("sphere_scene", 1.5)
+    tab = hs.flat.contents.perlin[0]
+    got = np.array([[tab.rand_vec[i][k] for k in range(3)] for i in range(3)], np.float32)
+    assert got.view(np.uint32).tolist() == K15_RAND_VEC
+    assert list(tab.perm_x)[:8] == K15_PERM_X and list(tab.perm_y)[:8] == K15_PERM_Y and list(tab.perm_z)[:8] == K15_PERM_Z
+    # the independent restatement
+    r = _PyXoshiro(1995)
+    v = [[r.gen_f32() * np.float32(2.0) + np.float32(-1.0) for _ in range(3)] for _ in range(256)]
+    assert np.array(v[:3], np.float32).view(np.uint32).tolist() == K15_RAND_VEC
+    p, perms = list(range(256)), []
+    for _ in range(3):
+        for i in range(255, 0, -1):
+            j = r.below_u32(i + 1)
+            p[i], p[j] = p[j], p[i]
+        perms.append(list(p))
+    assert [perms[0][:8], perms[1][:8], perms[2][:8]] == [K15_PERM_X, K15_PERM_Y, K15_PERM_Z]
+    assert sorted(perms[2]) == list(range(256))

@@ -7,7 +7,7 @@ name = sys.argv[1] if len(sys.argv) > 1 else "sphere_scene"
 w = int(sys.argv[2]) if len(sys.argv) > 2 else 1920
 h = int(sys.argv[3]) if len(sys.argv) > 3 else 1080
 spp = int(sys.argv[4]) if len(sys.argv) > 4 else 64
-modes = [int(m) for m in (sys.argv[5].split(",") if len(sys.argv) > 5 else "1,2,3".split(","))]
+modes = [int(m) for m in (sys.argv[5].split(",") if len(sys.argv) > 5 else "1,3".split(","))]
 hs = rt.HostScene(name, w / h)
 sc = rt.Scene(hs.flat, 0)
 for mode in modes:
