@@ -289,7 +289,9 @@ static void world_boxes(const RtFlatScene& fs, std::vector<uint32_t>& world, std
     ref.resize(world.size());
     std::vector<float> ext(world.size());
     for (size_t k = 0; k < world.size(); k++) {
-        ref[k] = box_to_world(fs, fs.prims[world[k]].xform, reference_bbox(fs, world[k]));
+        // (a medium's box is the union of its boundary boxes, which carry their full chains: already world space)
+        const RtPrim& wp = fs.prims[world[k]];
+        ref[k] = wp.kind == RT_PRIM_MEDIUM ? reference_bbox(fs, world[k]) : box_to_world(fs, wp.xform, reference_bbox(fs, world[k]));
         ext[k] = ref[k].extent_max();
     }
     std::vector<float> sorted_ext = ext;

@@ -69,7 +69,7 @@ int rt_comm_create(const uint8_t id_bytes[RT_COMM_UNIQUE_ID_BYTES], int n_ranks,
     c->comms = {nullptr};
     ncclUniqueId id;
     std::memcpy(&id, id_bytes, sizeof(id));
-    NCCL_TRY(ncclCommInitRank(&c->comms[0], n_ranks, id, rank));
+    if (n_ranks > 1) NCCL_TRY(ncclCommInitRank(&c->comms[0], n_ranks, id, rank));  // (one rank: no collective is ever issued)
     *out = c.release();
     return RT_OK;
 }
@@ -90,7 +90,7 @@ int rt_comm_create_all(const int* devices, int n_devices, RtComm** out) {
     c->first_rank = 0;
     c->devices.assign(devices, devices + n_devices);
     c->comms.assign((size_t)n_devices, nullptr);
-    NCCL_TRY(ncclCommInitAll(c->comms.data(), n_devices, devices));
+    if (n_devices > 1) NCCL_TRY(ncclCommInitAll(c->comms.data(), n_devices, devices));  // (one rank: no collective is ever issued)
     *out = c.release();
     return RT_OK;
 }

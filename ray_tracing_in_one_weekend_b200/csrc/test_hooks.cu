@@ -277,6 +277,49 @@ RT_TEST_API int rt_test_bvh_validate(const RtFlatScene* desc, uint32_t leaf_max,
         }
         node_box[n] = acc;
     }
+    // Leaf boxes of media and of primitives under wrappers: every corner of the (boundary) geometry, carried to world
+    // space with this hook's own transform code (object -> world = the wrappers undone innermost first:
+    // hitable.rs:413 `rec.p += offset`, 495-498 rotation by +theta), lies inside the box its leaf stores.
+    {
+        std::vector<uint32_t> world;
+        std::vector<Box6> ref, padded;
+        compute_world_boxes(*desc, world, ref, padded);
+        auto to_world = [&](uint32_t chain, float* p) {
+            const RtXformChain& ch = desc->xform_chains[chain];
+            for (int k = (int)ch.n_ops - 1; k >= 0; k--) {
+                const RtXformOp& op = desc->xform_ops[ch.first_op + k];
+                if (op.kind == RT_XF_TRANSLATE) {
+                    for (int a = 0; a < 3; a++) p[a] += op.v[a];
+                } else {
+                    const float sn = op.v[0], cs = op.v[1], x = p[0], z = p[2];
+                    p[0] = cs * x + sn * z;
+                    p[2] = -sn * x + cs * z;
+                }
+            }
+        };
+        auto check_geom = [&](const RtPrim& g, const Box6& box) -> bool {
+            for (int corner = 0; corner < 8; corner++) {
+                float p[3];
+                for (int a = 0; a < 3; a++) {
+                    if (g.kind == RT_PRIM_SPHERE || g.kind == RT_PRIM_MOVING_SPHERE) p[a] = g.g[a] + ((corner >> a & 1) ? 0.577f : -0.577f) * g.g[3];
+                    else p[a] = (corner >> a & 1) ? g.g[3 + a] : g.g[a];
+                }
+                to_world(g.xform, p);
+                for (int a = 0; a < 3; a++)
+                    if (p[a] < box.lo[a] - 1e-3f || p[a] > box.hi[a] + 1e-3f) return false;
+            }
+            return true;
+        };
+        for (size_t k = 0; k < world.size(); k++) {
+            const RtPrim& p = desc->prims[world[k]];
+            if (p.kind == RT_PRIM_MEDIUM) {
+                for (uint32_t j = 0; j < p.aux1; j++)
+                    if (!check_geom(desc->prims[p.aux0 + j], padded[k])) return fail(RT_ERR_ARG, "bvh: medium boundary outside the medium's box");
+            } else if (!check_geom(p, padded[k])) {
+                return fail(RT_ERR_ARG, "bvh: primitive outside its box");
+            }
+        }
+    }
     for (uint32_t i = 0; i < desc->n_prims; i++) {
         int want = (desc->prims[i].flags & RT_PRIM_FLAG_BOUNDARY_ONLY) ? 0 : 1;
         if (seen[i] != want) return fail(RT_ERR_ARG, "bvh: primitive referenced " + std::to_string(seen[i]) + " times");

@@ -87,7 +87,8 @@ def test_cover_100k_motion_scene_shape(rtlib):
     assert f.camera.time0 == 0.0 and f.camera.time1 == 1.0
 
 
-@pytest.mark.parametrize("name", ["test_sphere", "sphere_scene", "cornell_box", "final_scene", "cover_4k_motion", "pbr_ibl"])
+@pytest.mark.parametrize("name", ["test_sphere", "sphere_scene", "cornell_box", "final_scene", "cover_4k_motion", "pbr_ibl",
+                                  "smoke_instances", "cornell_box_solid"])
 @pytest.mark.parametrize("leaf_max", [1, 4, 8])
 def test_bvh_invariants(rtlib, name, leaf_max):
     lib = rtlib.load_test_library()
