@@ -25,6 +25,7 @@ CUDA_SRCS = ["rtgpu.cu", "rt_comm.cu", "gpu_bvh.cu"]
 TEST_SRCS = ["test_hooks.cu"]
 CTA_FEATURE_SETS = [0, 4, 8, 9, 11, 15]  # cta_inst.cu is compiled once per set (kernels_cta.cuh)
 CTA_NO_PBR_SETS = [0, 4]  # ... and once more without the pbr.rs shading class for the sphere-only sets
+CTA_FLAT_SETS = [0, 8, 9, 11]  # ... and the tiny-scene builds (warp-uniform primitive loop instead of the BVH traversal)
 HEADERS = ["scene_api.hpp", "bvh_build.hpp", "device_types.h", "rt_device.cuh", "kernels.cuh", "kernels_cta.cuh", "gpu_bvh.hpp", "rt_internal.hpp",
            os.path.join("..", "..", "include", "rtgpu.h")]
 
@@ -83,6 +84,11 @@ def build_all(force: bool = False, verbose: bool = False, extra: tuple = (), out
         obj = os.path.join(obj_dir, f"cta_f{f}_m3f.o")
         if force or _stale(obj, [os.path.join(CSRC, "cta_inst.cu")] + hdrs):
             jobs.append([NVCC] + nvcc_flags + [f"-DRT_CTA_F={f}", "-DRT_CTA_CLS_MASK=0x3f", "-DRT_CTA_SUFFIX=_m3f", "-c", "cta_inst.cu", "-o", obj])
+        objs.append(obj)
+    for f in CTA_FLAT_SETS:
+        obj = os.path.join(obj_dir, f"cta_f{f}_flat.o")
+        if force or _stale(obj, [os.path.join(CSRC, "cta_inst.cu")] + hdrs):
+            jobs.append([NVCC] + nvcc_flags + [f"-DRT_CTA_F={f}", "-DRT_CTA_FLAT=1", "-DRT_CTA_SUFFIX=_flat", "-c", "cta_inst.cu", "-o", obj])
         objs.append(obj)
     if jobs:  # the CUDA units are independent: compile them side by side
         from concurrent.futures import ThreadPoolExecutor

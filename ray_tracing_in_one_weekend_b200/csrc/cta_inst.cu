@@ -11,7 +11,8 @@
 #define RT_CAT2(a, b) a##b
 #define RT_CAT(a, b) RT_CAT2(a, b)
 
-#ifdef RT_CTA_SUFFIX  // e.g. -DRT_CTA_CLS_MASK=0x3f -DRT_CTA_SUFFIX=_m3f: the build without the pbr.rs shading class
+#ifdef RT_CTA_SUFFIX  // e.g. -DRT_CTA_CLS_MASK=0x3f -DRT_CTA_SUFFIX=_m3f: the build without the pbr.rs shading class;
+                      //      -DRT_CTA_FLAT=1 -DRT_CTA_SUFFIX=_flat: the tiny-scene build (warp-uniform primitive loop)
 #define RT_CTA_ENTRY RT_CAT(RT_CAT(cta_kernel_f, RT_CTA_F), RT_CTA_SUFFIX)
 #else
 #define RT_CTA_ENTRY RT_CAT(cta_kernel_f, RT_CTA_F)
@@ -20,7 +21,7 @@
 namespace rtb {
 void* RT_CTA_ENTRY(bool count, int* threads) {
     if (threads) *threads = CTA_THREADS;
-    return count ? (void*)k_render_cta<(uint32_t)RT_CTA_F, true, (uint32_t)RT_CTA_CLS_MASK>
-                 : (void*)k_render_cta<(uint32_t)RT_CTA_F, false, (uint32_t)RT_CTA_CLS_MASK>;
+    return count ? (void*)k_render_cta<(uint32_t)RT_CTA_F, true, (uint32_t)RT_CTA_CLS_MASK, (RT_CTA_FLAT) != 0>
+                 : (void*)k_render_cta<(uint32_t)RT_CTA_F, false, (uint32_t)RT_CTA_CLS_MASK, (RT_CTA_FLAT) != 0>;
 }
 }  // namespace rtb

@@ -220,7 +220,11 @@ RT_DEV void cta_retire(const CtaPool& P, CtaLane& L, uint32_t* s_cnt) {
     L.pid = CTA_NONE;
 }
 
-template <uint32_t F, bool COUNT, uint32_t MASK>
+// FLAT: the traverse phase runs the warp-uniform primitive loop (flat_closest_hit) instead of the BVH traversal.
+#ifndef RT_CTA_FLAT
+#define RT_CTA_FLAT 0
+#endif
+template <uint32_t F, bool COUNT, uint32_t MASK, bool FLAT = false>
 __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(DeviceScene sc, CtaArgs a) {
     extern __shared__ float4 cta_smem[];
     __shared__ uint32_t s_cnt[8];  // per-class queue lengths of this iteration
@@ -261,7 +265,7 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
     uint32_t n_rays = 0, n_shade = 0;
     unsigned long long cls_total[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // thread 0, COUNT builds only
     TravCounters tc;
-    uint2 stack[STACK_SIZE];
+    uint2 stack[FLAT ? 1 : STACK_SIZE];
     if (tid == 0) {
 #pragma unroll
         for (int c = 0; c < 8; c++) s_cnt[c] = 0u;
@@ -341,6 +345,30 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
             L.xc.chain = 0;
             L.xc.ro = L.ray;
             L.rng.state = 0;
+            if (FLAT) {
+                // Tiny scenes: 32 todo entries per warp at a time (scattered and regenerated alike), every lane walks
+                // the same primitive list — no refill, no stack, no divergence between node and leaf code.
+                (void)stack;
+                const uint32_t n_todo = n_surv + n_regen;
+                for (;;) {
+                    uint32_t base = 0;
+                    if (lane == 0) base = atomicAdd(&s_next, 32u);
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    if (base >= n_todo) break;
+                    bool active = base + lane < n_todo;
+                    if (active) {
+                        cta_fetch<F>(P, P.todo[base + lane], L);
+                        n_rays++;
+                        active = L.ts.cur != TRAV_NONE;  // main.rs:39: a non-unit direction loses the path
+                    }
+                    flat_closest_hit<F, COUNT>(sc, L.ray, 1e-3f, L.ts, L.rng, false, active, &tc);
+                    if (base + lane < n_todo) {
+                        L.ts.cur = TRAV_NONE;
+                        cta_retire<F>(P, L, s_cnt);
+                    }
+                    __syncwarp();
+                }
+            } else {
 #if RT_CTA_ONE_LOOP
             // One instance of the traversal loop serves both parts of the todo list (instruction-cache footprint):
             // stage 0 = scattered rays, idle lanes refilled from the block's counter; stage 1 = camera rays, a
@@ -439,6 +467,7 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
                 __syncwarp();
             }
 #endif
+            }  // !FLAT
         }
 #if RT_CTA_PROFILE
         if (lane == 0) pf_work[0] += clock64() - pf_t;
@@ -537,10 +566,22 @@ void* cta_kernel_f11(bool count, int* threads);
 void* cta_kernel_f15(bool count, int* threads);
 void* cta_kernel_f0_m3f(bool count, int* threads);  // the same without the pbr.rs shading class
 void* cta_kernel_f4_m3f(bool count, int* threads);
+void* cta_kernel_f0_flat(bool count, int* threads);  // FLAT builds (tiny scenes): spheres; + rects; + transforms; + media
+void* cta_kernel_f8_flat(bool count, int* threads);
+void* cta_kernel_f9_flat(bool count, int* threads);
+void* cta_kernel_f11_flat(bool count, int* threads);
 
 // The kernel of the smallest built feature set that covers `features`.
-inline void* cta_kernel_for(uint32_t features, uint32_t class_mask, bool count, uint32_t* built, int* threads) {
+inline void* cta_kernel_for(uint32_t features, uint32_t class_mask, bool count, bool flat, uint32_t* built, int* threads) {
     struct E { uint32_t f; void* (*fn)(bool, int*); };
+    if (flat) {
+        const E flat_table[] = {{0u, cta_kernel_f0_flat}, {8u, cta_kernel_f8_flat}, {9u, cta_kernel_f9_flat}, {11u, cta_kernel_f11_flat}};
+        for (const E& e : flat_table)
+            if ((features & ~e.f) == 0u) {
+                if (built) *built = e.f;
+                return e.fn(count, threads);
+            }
+    }
     if (!((class_mask >> CLS_PBR) & 1u)) {  // no pbr.rs material in the scene
         if (features == 0u) { if (built) *built = 0u; return cta_kernel_f0_m3f(count, threads); }
         if (features == 4u) { if (built) *built = 4u; return cta_kernel_f4_m3f(count, threads); }

@@ -578,6 +578,10 @@ int rt_scene_create_ex(const RtFlatScene* desc, int device, uint32_t flags, RtSc
     const size_t off_grad = reserve(n_grad * sizeof(float4), (size_t)std::max(tex_align, 256));
     const size_t off_perm = reserve(n_perm, 256);
     const size_t off_imgtab = reserve(desc->n_images * sizeof(DevImage), 256);
+    std::vector<uint32_t> flat_order;  // world primitives in flat (visitation) order -> device index
+    for (uint32_t i = 0; i < desc->n_prims; i++)
+        if (!(desc->prims[i].flags & RT_PRIM_FLAG_BOUNDARY_ONLY)) flat_order.push_back(flat_to_dev[i]);
+    const size_t off_flat = reserve(flat_order.size() * sizeof(uint32_t), 256);
     std::vector<size_t> off_img(desc->n_images), pitch_img(desc->n_images);
     for (uint32_t i = 0; i < desc->n_images; i++) {
         pitch_img[i] = align_up((size_t)desc->images[i].width * 4, (size_t)std::max(pitch_align, 128));
@@ -600,6 +604,7 @@ int rt_scene_create_ex(const RtFlatScene* desc, int device, uint32_t flags, RtSc
     put(off_chains, chains.data(), chains.size() * sizeof(DevXformChain));
     put(off_mats, mats.data(), mats.size() * sizeof(DevMaterial));
     put(off_texs, texs.data(), texs.size() * sizeof(DevTexture));
+    put(off_flat, flat_order.data(), flat_order.size() * sizeof(uint32_t));
     {  // Perlin tables: 256 float4 gradients + 768 permutation bytes per table
         float4* grad = reinterpret_cast<float4*>(h + off_grad);
         uint8_t* perm = reinterpret_cast<uint8_t*>(h + off_perm);
@@ -674,6 +679,7 @@ int rt_scene_create_ex(const RtFlatScene* desc, int device, uint32_t flags, RtSc
     s->ds.perlin_grad_lin = reinterpret_cast<const float4*>(dbase + off_grad);
     s->ds.perlin_perm = reinterpret_cast<const uint8_t*>(dbase + off_perm);
     s->ds.images = reinterpret_cast<const DevImage*>(dbase + off_imgtab);
+    s->ds.flat_order = reinterpret_cast<const uint32_t*>(dbase + off_flat);
     s->ds.n_perlin = desc->n_perlin;
     s->ds.sky = DevSky{desc->sky.kind, desc->sky.image, desc->sky.color[0], desc->sky.color[1], desc->sky.color[2]};
     const RtCamera& c = desc->camera;
@@ -807,7 +813,9 @@ static int cta_plan(RtScene* s, bool count, const CtaPlan** out) {
         // worth of paths less keeps the block inside the same carve-out (+2..8 % on those scenes).
         const bool media = (s->features & F_MEDIA) != 0;
         p.stage_perlin = !media && (s->class_mask >> CLS_DIFFUSE_PERLIN & 1u) && s->ds.n_perlin > 0 ? 1u : 0u;
-        void* fn = cta_kernel_for(s->features, s->knob_full_kernel ? 0x7fu : s->class_mask, count, nullptr, &p.threads);
+        // Tiny scenes (<= 32 world primitives, no moving spheres): the warp-uniform primitive loop replaces the BVH
+        p.flat = (s->features & F_MOTION) == 0u && s->n_world_prims <= (uint32_t)(s->knob_flat >= 0 ? s->knob_flat : 32);
+        void* fn = cta_kernel_for(s->features, s->knob_full_kernel ? 0x7fu : s->class_mask, count, p.flat, nullptr, &p.threads);
         const int dflt_paths = p.stage_perlin ? 1120 : 1152;
         p.n_paths = (uint32_t)std::max(32, std::min(4096, s->knob_paths > 0 ? s->knob_paths : dflt_paths)) & ~31u;
         p.refill_idle = (uint32_t)std::max(1, std::min(32, s->knob_refill));

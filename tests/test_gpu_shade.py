@@ -90,6 +90,9 @@ def test_textures_and_sky_match_oracle(rtlib, oracle, scene_name):
     uv = rng.random((n, 2), dtype=np.float32)
     uv[:8] = [[0, 0], [1, 1], [0, 1], [1, 0], [-0.5, 2.0], [0.5, 0.5], [0.999999, 0.000001], [np.nan, 0.3]]
     p = (rng.random((n, 3), dtype=np.float32) * 30 - 15).astype(np.float32)
+    # lattice coordinates beyond 2^31 / 2^63, infinities and NaN: `floor() as isize` saturates, `& 255` keeps 8 bits
+    p[8:16] = [[3e9, 0.5, -7e9], [1e20, -1e20, 2.5], [np.inf, 0.25, 0.5], [np.nan, 1.0, 2.0], [-2147483648.0, 2147483648.0, 0.25],
+               [2147483520.0, -2147483520.0, 1.5], [-np.inf, 3.0, -3.0], [9.3e18, -9.3e18, 0.75]]
     seen = set()
     for t in range(flat.n_textures):
         kind = flat.textures[t].kind
