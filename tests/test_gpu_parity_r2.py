@@ -140,7 +140,8 @@ def test_closest_hit_with_media_and_injected_numbers(rtlib, oracle, name, w, h):
     same = ~diff & (want["prim"] >= 0)
     med = same & is_medium[want["prim"]]
     geo = same & ~is_medium[want["prim"]]
-    assert med.sum() > n // 100, f"{name}: only {med.sum()} medium hits"
+    if name != "final_scene":  # (its one medium sits inside a glass sphere: primary rays meet the glass first)
+        assert med.sum() > n // 100, f"{name}: only {med.sum()} medium hits"
     for f in ("t", "p", "n"):
         assert np.array_equal(got[f][geo].view(np.uint32), want[f][geo].view(np.uint32)), f
     np.testing.assert_allclose(got["t"][med], want["t"][med], rtol=2e-6)
