@@ -36,6 +36,9 @@ namespace rtb {
 // need ~100 registers per thread; at 384 threads x 2 blocks (80 registers) they carry 320-370 B of spills, at 320
 // threads (96 registers, 20 warps per SM) 56 B — final_scene +15 %, cornell_box +7 % (B200, 1080p).  Every other
 // set fits 80 registers and prefers the four extra warps (cornell_box_solid, cover_100k_motion: -1..-4 % at 320/352).
+#if !defined(RT_CTA_THREADS) && defined(RT_CTA_FLAT_THREADS) && defined(RT_CTA_FLAT) && RT_CTA_FLAT
+#define RT_CTA_THREADS RT_CTA_FLAT_THREADS  // (development: block size of the tiny-scene builds only)
+#endif
 #ifndef RT_CTA_THREADS
 #if defined(RT_CTA_F) && ((RT_CTA_F) & 2)
 #define RT_CTA_THREADS 320
