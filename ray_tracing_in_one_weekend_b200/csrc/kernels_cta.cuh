@@ -36,11 +36,17 @@ namespace rtb {
 // need ~100 registers per thread; at 384 threads x 2 blocks (80 registers) they carry 320-370 B of spills, at 320
 // threads (96 registers, 20 warps per SM) 56 B — final_scene +15 %, cornell_box +7 % (B200, 1080p).  Every other
 // set fits 80 registers and prefers the four extra warps (cornell_box_solid, cover_100k_motion: -1..-4 % at 320/352).
-#if !defined(RT_CTA_THREADS) && defined(RT_CTA_FLAT_THREADS) && defined(RT_CTA_FLAT) && RT_CTA_FLAT
+// FLAT: the traverse phase runs the warp-uniform primitive loop (flat_closest_hit) instead of the BVH traversal —
+// the tiny-scene builds (cta_inst.cu -DRT_CTA_FLAT=1 -DRT_CTA_SUFFIX=_flat).  Without a traversal stack and slab
+// constants even the media set fits 80 registers (36 B of spills): 384 threads, cornell_box +14 % over 320.
+#ifndef RT_CTA_FLAT
+#define RT_CTA_FLAT 0
+#endif
+#if !defined(RT_CTA_THREADS) && defined(RT_CTA_FLAT_THREADS) && RT_CTA_FLAT
 #define RT_CTA_THREADS RT_CTA_FLAT_THREADS  // (development: block size of the tiny-scene builds only)
 #endif
 #ifndef RT_CTA_THREADS
-#if defined(RT_CTA_F) && ((RT_CTA_F) & 2)
+#if defined(RT_CTA_F) && ((RT_CTA_F) & 2) && !RT_CTA_FLAT
 #define RT_CTA_THREADS 320
 #else
 #define RT_CTA_THREADS 384
@@ -223,10 +229,6 @@ RT_DEV void cta_retire(const CtaPool& P, CtaLane& L, uint32_t* s_cnt) {
     L.pid = CTA_NONE;
 }
 
-// FLAT: the traverse phase runs the warp-uniform primitive loop (flat_closest_hit) instead of the BVH traversal.
-#ifndef RT_CTA_FLAT
-#define RT_CTA_FLAT 0
-#endif
 template <uint32_t F, bool COUNT, uint32_t MASK, bool FLAT = false>
 __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(DeviceScene sc, CtaArgs a) {
     extern __shared__ float4 cta_smem[];
