@@ -64,7 +64,7 @@ fn main() {
     }
     let lib = out.join("librtgpu.so");
     run(Command::new(&nvcc).arg("-shared").arg("-o").arg(&lib).args(&objs)
-        .args(["-gencode", "arch=compute_100a,code=sm_100a", "-lz", "-lnccl", "-Xlinker"])
+        .args(["-gencode", "arch=compute_100a,code=sm_100a", "-lz", "-ldl", "-Xlinker"])
         .arg(format!("--version-script={}", Path::new(&csrc).join("exports.map").display())));
     println!("cargo:rustc-link-search=native={}", out.display());
     println!("cargo:rustc-link-lib=dylib=rtgpu");

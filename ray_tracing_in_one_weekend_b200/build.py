@@ -95,7 +95,7 @@ def build_all(force: bool = False, verbose: bool = False, extra: tuple = (), out
         with ThreadPoolExecutor(max_workers=min(len(jobs), os.cpu_count() or 4)) as ex:
             log.extend(ex.map(_run, jobs))
     # exports.map: the dynamic symbol table holds the rt_* entry points and nothing else (no C++ internals)
-    link = ["-gencode", "arch=compute_100a,code=sm_100a", "-lz", "-lnccl", "-Xlinker", "--version-script=" + os.path.join(CSRC, "exports.map")]
+    link = ["-gencode", "arch=compute_100a,code=sm_100a", "-lz", "-ldl", "-Xlinker", "--version-script=" + os.path.join(CSRC, "exports.map")]
     if force or _stale(lib, objs + [os.path.join(CSRC, "exports.map")]):
         log.append(_run([NVCC, "-shared", "-o", lib] + objs + link))
     if force or _stale(test_lib, objs + test_objs + [os.path.join(CSRC, "exports.map")]):

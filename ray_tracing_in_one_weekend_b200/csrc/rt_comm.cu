@@ -22,11 +22,61 @@ using namespace rtb;
 
 static_assert(sizeof(ncclUniqueId) == RT_COMM_UNIQUE_ID_BYTES, "RT_COMM_UNIQUE_ID_BYTES must match ncclUniqueId");
 
+// NCCL is bound at RUN time, when the first multi-rank communicator is made (dlopen by SONAME): librtgpu.so itself
+// carries no NCCL dependency, so a single-GPU host needs no NCCL installed, and a process that also hosts another
+// NCCL user (PyTorch bundles its own libnccl.so.2) ends up with ONE copy — whichever was loaded first.
+#include <dlfcn.h>
+namespace {
+struct NcclApi {
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommInitAll)(ncclComm_t*, int, const int*) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*Reduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+    std::string error;  // why binding failed (empty: bound)
+    bool bound = false;
+};
+NcclApi& nccl() {
+    static NcclApi api = [] {
+        NcclApi a;
+        void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) {
+            a.error = std::string("cannot load libnccl.so.2: ") + dlerror();
+            return a;
+        }
+        auto sym = [&](const char* name) -> void* {
+            void* p = dlsym(h, name);
+            if (!p && a.error.empty()) a.error = std::string("libnccl lacks ") + name;
+            return p;
+        };
+        a.GetUniqueId = reinterpret_cast<decltype(a.GetUniqueId)>(sym("ncclGetUniqueId"));
+        a.CommInitRank = reinterpret_cast<decltype(a.CommInitRank)>(sym("ncclCommInitRank"));
+        a.CommInitAll = reinterpret_cast<decltype(a.CommInitAll)>(sym("ncclCommInitAll"));
+        a.CommDestroy = reinterpret_cast<decltype(a.CommDestroy)>(sym("ncclCommDestroy"));
+        a.Reduce = reinterpret_cast<decltype(a.Reduce)>(sym("ncclReduce"));
+        a.GroupStart = reinterpret_cast<decltype(a.GroupStart)>(sym("ncclGroupStart"));
+        a.GroupEnd = reinterpret_cast<decltype(a.GroupEnd)>(sym("ncclGroupEnd"));
+        a.GetErrorString = reinterpret_cast<decltype(a.GetErrorString)>(sym("ncclGetErrorString"));
+        a.bound = a.error.empty();
+        return a;
+    }();
+    return api;
+}
+}  // namespace
+#define NCCL_BOUND()                                                          \
+    do {                                                                      \
+        if (!nccl().bound) return rt_fail(RT_ERR_NCCL, nccl().error);         \
+    } while (0)
+
 #define NCCL_TRY(expr)                                                                                      \
     do {                                                                                                    \
         ncclResult_t r__ = (expr);                                                                          \
         if (r__ != ncclSuccess)                                                                             \
-            return rt_fail(RT_ERR_NCCL, std::string(#expr) + ": " + ncclGetErrorString(r__));              \
+            return rt_fail(RT_ERR_NCCL, std::string(#expr) + ": " + nccl().GetErrorString(r__));           \
     } while (0)
 
 struct RtComm {
@@ -36,9 +86,9 @@ struct RtComm {
     std::vector<ncclComm_t> comms;   // one communicator per local device
     ~RtComm() {
         for (size_t i = 0; i < comms.size(); i++) {
-            if (!comms[i]) continue;
+            if (!comms[i] || !nccl().bound) continue;
             cudaSetDevice(devices[i]);
-            ncclCommDestroy(comms[i]);
+            nccl().CommDestroy(comms[i]);
         }
     }
 };
@@ -48,8 +98,9 @@ extern "C" {
 
 int rt_comm_unique_id(uint8_t out_id[RT_COMM_UNIQUE_ID_BYTES]) {
     if (!out_id) return rt_fail(RT_ERR_ARG, "NULL argument");
+    NCCL_BOUND();
     ncclUniqueId id;
-    NCCL_TRY(ncclGetUniqueId(&id));
+    NCCL_TRY(nccl().GetUniqueId(&id));
     std::memcpy(out_id, &id, sizeof(id));
     return RT_OK;
 }
@@ -69,7 +120,10 @@ int rt_comm_create(const uint8_t id_bytes[RT_COMM_UNIQUE_ID_BYTES], int n_ranks,
     c->comms = {nullptr};
     ncclUniqueId id;
     std::memcpy(&id, id_bytes, sizeof(id));
-    if (n_ranks > 1) NCCL_TRY(ncclCommInitRank(&c->comms[0], n_ranks, id, rank));  // (one rank: no collective is ever issued)
+    if (n_ranks > 1) {
+        NCCL_BOUND();
+        NCCL_TRY(nccl().CommInitRank(&c->comms[0], n_ranks, id, rank));
+    }  // (one rank: no collective is ever issued)
     *out = c.release();
     return RT_OK;
 }
@@ -90,7 +144,10 @@ int rt_comm_create_all(const int* devices, int n_devices, RtComm** out) {
     c->first_rank = 0;
     c->devices.assign(devices, devices + n_devices);
     c->comms.assign((size_t)n_devices, nullptr);
-    if (n_devices > 1) NCCL_TRY(ncclCommInitAll(c->comms.data(), n_devices, devices));  // (one rank: no collective is ever issued)
+    if (n_devices > 1) {
+        NCCL_BOUND();
+        NCCL_TRY(nccl().CommInitAll(c->comms.data(), n_devices, devices));
+    }  // (one rank: no collective is ever issued)
     *out = c.release();
     return RT_OK;
 }
@@ -128,16 +185,16 @@ int rt_render_reduce_device(RtScene* const* scenes, RtComm* comm, const RtRender
     }
     // (2) ONE sum-reduce to rank 0, in place, stream-ordered behind the render kernels
     if (comm->n_ranks > 1) {
-        NCCL_TRY(ncclGroupStart());
+        NCCL_TRY(nccl().GroupStart());
         for (int i = 0; i < n_local; i++) {
             cudaStream_t st = (streams && streams[i]) ? (cudaStream_t)streams[i] : scenes[i]->stream;
-            ncclResult_t r = ncclReduce(accum[i], accum[i], nf, ncclFloat, ncclSum, 0, comm->comms[i], st);
+            ncclResult_t r = nccl().Reduce(accum[i], accum[i], nf, ncclFloat, ncclSum, 0, comm->comms[i], st);
             if (r != ncclSuccess) {
-                ncclGroupEnd();
-                return rt_fail(RT_ERR_NCCL, std::string("ncclReduce: ") + ncclGetErrorString(r));
+                nccl().GroupEnd();
+                return rt_fail(RT_ERR_NCCL, std::string("ncclReduce: ") + nccl().GetErrorString(r));
             }
         }
-        NCCL_TRY(ncclGroupEnd());
+        NCCL_TRY(nccl().GroupEnd());
     }
     // (3) the root divides by the frame's sample count (c /= samples_per_pixel, src/main.rs:98)
     if (comm->first_rank == 0) {
