@@ -105,21 +105,21 @@ inline size_t cta_smem_bytes(uint32_t n, bool perlin) {
 }
 
 struct CtaPool {
-    float4* o;       // o.xyz, time                       (a slot waiting for its camera ray: o.x = bits(sample index))
+    float4* o;       // o.xyz, time
     float4* d;       // d.xyz, bits(depth | alive << 31)
     float4* b;       // throughput rgb, bits(pixel)
     uint4* m;        // rng.lo, rng.hi, bits(t), prim
-    uint16_t* list;  // [CLS_COUNT][N] path ids per shade queue
-    uint16_t* cam;   // [N] slots that start a NEW path next iteration (their camera ray is generated when a warp fetches them)
-    uint16_t* todo;  // [N] slots whose path scattered: traverse next
+    uint16_t* list;  // [CLS_COUNT][N] path ids per shading class
+    uint16_t* dead;  // [N] path ids to regenerate
+    uint16_t* todo;  // [N] path ids to traverse next: scattered paths (in shading order), then the regenerated ones
     const float4* perlin;  // Perlin table 0 (256 gradients, then 768 permutation bytes) or nullptr
     uint32_t N;
 };
 
-// One queue entry of class CLS: the body of ray_color for a hit (main.rs:45-56) or a miss (main.rs:58).  Returns whether
-// the path lives on (then its scattered ray is back in the slot and the slot is on the todo list).
+// One queue entry of class CLS: the body of ray_color for a hit (main.rs:45-56) or a miss (main.rs:58).
 template <uint32_t F, int CLS>
-RT_DEV bool cta_shade_item(const DeviceScene& sc, const CtaArgs& a, const CtaPool& P, uint32_t pid, uint32_t* s_ntodo, uint32_t& n_shade) {
+RT_DEV void cta_shade_item(const DeviceScene& sc, const CtaArgs& a, const CtaPool& P, uint32_t pid, uint32_t* s_ndead,
+                           uint32_t* s_ntodo, uint32_t& n_shade) {
     const float4 rd = P.d[pid], bt = P.b[pid];
     Ray ray;
     ray.d = mk3(rd.x, rd.y, rd.z);
@@ -171,8 +171,11 @@ RT_DEV bool cta_shade_item(const DeviceScene& sc, const CtaArgs& a, const CtaPoo
         uint2* st = reinterpret_cast<uint2*>(P.m + pid);
         *st = make_uint2((uint32_t)rng.state, (uint32_t)(rng.state >> 32));
         P.todo[atomicAdd(s_ntodo, 1u)] = (uint16_t)pid;
+    } else {
+        P.d[pid].w = __uint_as_float(0u);
+        const uint32_t pos = atomicAdd(s_ndead, 1u);
+        P.dead[pos] = (uint16_t)pid;
     }
-    return alive;
 }
 
 // Traversal registers of one lane.
@@ -185,57 +188,30 @@ struct CtaLane {
     PcgRng rng;
 };
 
-// Set the lane's traversal up for the ray it holds (main.rs:39-44).
-template <uint32_t F, bool FLAT>
-RT_DEV void cta_start(const CtaPool& P, CtaLane& L) {
-    L.ts.init(3.402823466e+38f);
-    if (F & F_XFORM) {
-        L.xc.chain = 0;
-        L.xc.ro = L.ray;
-    }
-    if (vec3a_near_one(L.ray.d)) {
-        if (!FLAT) L.rs.init(L.ray);
-    } else {
-        // main.rs:39: a non-unit direction loses the path; it retires as a miss with zero throughput
-        P.b[L.pid] = make_float4(0.0f, 0.0f, 0.0f, P.b[L.pid].w);
-        L.ts.cur = TRAV_NONE;
-    }
-}
-
-// Load the scattered ray of pool slot `idx` into the lane.
-template <uint32_t F, bool FLAT>
+// Load the ray of pool slot `idx` into the lane and set its traversal up (main.rs:39-44).
+template <uint32_t F>
 RT_DEV void cta_fetch(const CtaPool& P, uint32_t idx, CtaLane& L) {
     const float4 rd = P.d[idx], ro = P.o[idx];
     L.pid = idx;
     L.ray.o = mk3(ro.x, ro.y, ro.z);
     L.ray.d = mk3(rd.x, rd.y, rd.z);
     L.ray.tm = ro.w;
+    L.ts.init(3.402823466e+38f);
+    if (F & F_XFORM) {
+        L.xc.chain = 0;
+        L.xc.ro = L.ray;
+    }
     if (F & F_MEDIA) {
         const uint2 st = *reinterpret_cast<const uint2*>(P.m + idx);
         L.rng.state = ((unsigned long long)st.y << 32) | st.x;
     }
-    cta_start<F, FLAT>(P, L);
-}
-
-// Pool slot `idx` starts a new path: the shade phase left its (pixel, sample) in the slot; generate the camera ray
-// (main.rs:88-93, camera.rs:40-46) into the slot and into the lane.  Warps fetch 32 consecutive entries of the camera
-// list = runs of neighbouring pixels of a row, so this code and the traversal that follows run coherently.
-template <uint32_t F, bool FLAT>
-RT_DEV void cta_fetch_camera(const DeviceScene& sc, const CtaArgs& a, const CtaPool& P, uint32_t idx, CtaLane& L) {
-    const uint32_t r = __float_as_uint(P.b[idx].w), s = __float_as_uint(P.o[idx].x);
-    const uint32_t py = r / a.width, px = r - py * a.width;
-    PcgRng rng;
-    rng.seed(a.seed, r, a.s_begin + s);
-    const float u = ((float)px + rng.next()) / (float)a.width;
-    const float v = ((float)py + rng.next()) / (float)a.height;
-    L.ray = camera_get_ray(sc.cam, u, v, rng);
-    L.pid = idx;
-    L.rng = rng;
-    P.o[idx] = make_float4(L.ray.o.x, L.ray.o.y, L.ray.o.z, L.ray.tm);
-    P.d[idx] = make_float4(L.ray.d.x, L.ray.d.y, L.ray.d.z, __uint_as_float(WF_ALIVE));
-    uint2* st = reinterpret_cast<uint2*>(P.m + idx);
-    *st = make_uint2((uint32_t)rng.state, (uint32_t)(rng.state >> 32));
-    cta_start<F, FLAT>(P, L);
+    if (vec3a_near_one(L.ray.d)) {
+        L.rs.init(L.ray);
+    } else {
+        // main.rs:39: a non-unit direction loses the path; it retires as a miss with zero throughput
+        P.b[idx] = make_float4(0.0f, 0.0f, 0.0f, P.b[idx].w);
+        L.ts.cur = TRAV_NONE;
+    }
 }
 
 // Traversal of the lane's ray is complete: hit record back to the slot, slot id to its class queue.
@@ -253,25 +229,16 @@ RT_DEV void cta_retire(const CtaPool& P, CtaLane& L, uint32_t* s_cnt) {
     L.pid = CTA_NONE;
 }
 
-// A block keeps up to two runs of RESERVED path indices (segment A is used up first): `len` paths starting at pixel r
-// of sample s.  Thread 0 tops the reservation up with one global atomicAdd per iteration while the other warps are
-// already traversing, so no thread ever waits for it.
-struct CtaSegments {
-    uint32_t len_a, r_a, s_a, len_b, r_b, s_b;
-};
-
 template <uint32_t F, bool COUNT, uint32_t MASK, bool FLAT = false>
 __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(DeviceScene sc, CtaArgs a) {
     extern __shared__ float4 cta_smem[];
-    // Counters are double-buffered by iteration parity where one phase fills what the next iteration's phase reads.
-    __shared__ uint32_t s_cnt[2][8];   // shade queue lengths: traverse(it) fills [it & 1], shade(it) reads it
-    __shared__ uint32_t s_ntodo[2];    // scattered paths: shade(it) appends to [(it + 1) & 1], traverse(it + 1) reads it
-    __shared__ uint32_t s_ncam[2];     // new paths, likewise
-    __shared__ uint32_t s_next;        // next entry of the todo list the traverse phase hands out
-    __shared__ uint32_t s_nextp;       // next entry of the camera list
-    __shared__ uint32_t s_chunk;       // next 32-entry chunk of the shade phase
-    __shared__ uint32_t s_alloc;       // path indices handed out by the current shade phase (offset into A then B)
-    __shared__ CtaSegments s_seg;      // constant during a shade phase
+    __shared__ uint32_t s_cnt[8];  // per-class queue lengths of this iteration
+    __shared__ uint32_t s_next;    // next entry of the scattered part of the todo list the traverse phase hands out
+    __shared__ uint32_t s_nextp;   // next entry of the regenerated (camera ray) part
+    __shared__ uint32_t s_chunk;   // next 32-entry chunk of the shade phase
+    __shared__ uint32_t s_ndead;   // entries of the dead list
+    __shared__ uint32_t s_ntodo;   // scattered paths appended to the todo list by the shade phase
+    __shared__ uint32_t s_nsurv, s_nregen, s_r0, s_s0;
 
     const uint32_t tid = threadIdx.x, lane = tid & 31u;
     const uint32_t N = a.n_paths;
@@ -281,8 +248,8 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
     P.b = P.d + N;
     P.m = reinterpret_cast<uint4*>(P.b + N);
     P.list = reinterpret_cast<uint16_t*>(P.m + N);
-    P.cam = P.list + (size_t)CLS_COUNT * N;
-    P.todo = P.cam + N;
+    P.dead = P.list + (size_t)CLS_COUNT * N;
+    P.todo = P.dead + N;
     P.N = N;
     P.perlin = nullptr;
     if (a.stage_perlin) {
@@ -292,113 +259,87 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
         P.perlin = dst;
     }
 
-    // Reserves the next N path indices of the launch: (valid paths among them, sample, pixel of the first).
-    auto reserve_block = [&](uint32_t& len, uint32_t& r, uint32_t& s) {
-        const unsigned long long base = atomicAdd(a.path_counter, (unsigned long long)N);
-        len = 0u;
-        r = s = 0u;
-        if (base < a.total_paths) {
-            const unsigned long long left = a.total_paths - base;
-            len = left < (unsigned long long)N ? (uint32_t)left : N;
-            s = (uint32_t)(base / a.per_sample);  // path index k -> (sample, pixel) = divmod(k, width * height), main.rs:84-93
-            r = (uint32_t)(base % a.per_sample);
-        }
-    };
-    // (pixel, sample) of the j-th path of the current reservation
-    auto path_of = [&](uint32_t j, uint32_t& r, uint32_t& s) {
-        if (j < s_seg.len_a) {
-            r = s_seg.r_a + j;
-            s = s_seg.s_a;
-        } else {
-            r = s_seg.r_b + (j - s_seg.len_a);
-            s = s_seg.s_b;
-        }
-        while (r >= a.per_sample) {
-            r -= a.per_sample;
-            s++;
-        }
-    };
-
-    bool exhausted = false;  // thread 0: the launch has no unreserved paths left
-    if (tid == 0) {
-        reserve_block(s_seg.len_a, s_seg.r_a, s_seg.s_a);
-        s_seg.len_b = s_seg.r_b = s_seg.s_b = 0u;
-        exhausted = s_seg.len_a < N;
-#pragma unroll
-        for (int c = 0; c < 8; c++) s_cnt[0][c] = s_cnt[1][c] = 0u;
-        s_ntodo[0] = s_ntodo[1] = 0u;
-        s_ncam[0] = s_seg.len_a;  // every slot starts a path in iteration 0 ...
-        s_ncam[1] = 0u;
-        s_alloc = s_seg.len_a;    // ... which uses up the first reservation
-        s_next = s_nextp = s_chunk = 0u;
-    }
-    __syncthreads();
     for (uint32_t i = tid; i < N; i += CTA_THREADS) {
         P.d[i] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(0u));
-        if (i < s_seg.len_a) {
-            uint32_t r, s;
-            path_of(i, r, s);
-            P.b[i] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(r));
-            P.o[i].x = __uint_as_float(s);
-            P.cam[i] = (uint16_t)i;
-        }
+        P.dead[i] = (uint16_t)i;
+    }
+    if (tid == 0) {
+        s_ndead = N;  // every slot "dies" once before the first iteration
+        s_ntodo = 0u;
     }
     uint32_t n_rays = 0, n_shade = 0;
     unsigned long long cls_total[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // thread 0, COUNT builds only
     TravCounters tc;
     uint2 stack[FLAT ? 1 : STACK_SIZE];
+    if (tid == 0) {
+#pragma unroll
+        for (int c = 0; c < 8; c++) s_cnt[c] = 0u;
+    }
+    __syncthreads();
 
 #if RT_CTA_PROFILE
-    long long pf_phase[4] = {0, 0, 0, 0};  // thread 0: wall cycles of bookkeeping, traverse, shade (incl. barrier waits), iterations
+    long long pf_phase[4] = {0, 0, 0, 0};  // thread 0: wall cycles of D+regen, traverse, shade (incl. barrier waits), iterations
     long long pf_work[2] = {0, 0};         // lane 0 of every warp: own work cycles in traverse, shade
     long long pf_t = clock64();
 #endif
-    for (uint32_t it = 0;; it++) {
-        const uint32_t cur = it & 1u, nxt = cur ^ 1u;
-        __syncthreads();
-        const uint32_t n_surv = s_ntodo[cur], n_cam = s_ncam[cur];
-        if (n_surv + n_cam == 0u) break;
-        // ================================================================== bookkeeping (thread 0, off the critical path)
+    for (;;) {
+        // ================================================================== D: regenerate ended paths
         if (tid == 0) {
-            // the previous shade phase handed out `used` reserved paths: advance the segments past them
-            uint32_t used = min(s_alloc, s_seg.len_a + s_seg.len_b);
-            CtaSegments g = s_seg;
-            if (used >= g.len_a) {
-                used -= g.len_a;
-                g.len_a = g.len_b - used;
-                g.r_a = g.r_b + used;
-                g.s_a = g.s_b;
-                g.len_b = 0u;
-            } else {
-                g.len_a -= used;
-                g.r_a += used;
+            const uint32_t n_dead = s_ndead;
+            uint32_t n_regen = 0;
+            if (n_dead) {
+                const unsigned long long base = atomicAdd(a.path_counter, (unsigned long long)n_dead);
+                if (base < a.total_paths) {
+                    const unsigned long long left = a.total_paths - base;
+                    n_regen = left < (unsigned long long)n_dead ? (uint32_t)left : n_dead;
+                    s_s0 = (uint32_t)(base / a.per_sample);
+                    s_r0 = (uint32_t)(base % a.per_sample);
+                }
             }
-            while (g.r_a >= a.per_sample) {
-                g.r_a -= a.per_sample;
-                g.s_a++;
-            }
-            if (g.len_b == 0u && g.len_a < N && !exhausted) {  // top up: the shade phase may need up to N new paths
-                reserve_block(g.len_b, g.r_b, g.s_b);
-                exhausted = g.len_b < N;
-            }
-            s_seg = g;
-            s_alloc = 0u;
+            s_nregen = n_regen;
+            s_nsurv = s_ntodo;
+            s_ntodo = 0u;
+            s_ndead = 0u;
+            s_next = 0u;
+            s_nextp = 0u;
             s_chunk = 0u;
-            s_ntodo[nxt] = 0u;
-            s_ncam[nxt] = 0u;
 #pragma unroll
             for (int c = 0; c < 8; c++) {
-                if (COUNT) cls_total[c] += s_cnt[nxt][c];
-                s_cnt[nxt][c] = 0u;
+                if (COUNT) cls_total[c] += s_cnt[c];
+                s_cnt[c] = 0u;
             }
         }
+        __syncthreads();
+        const uint32_t n_regen = s_nregen, n_surv = s_nsurv;
+        if (n_regen + n_surv == 0u) break;
+        for (uint32_t i = tid; i < n_regen; i += CTA_THREADS) {
+            const uint32_t pid = P.dead[i];
+            // path index k = base + i  ->  (sample, pixel) = divmod(k, width * height), main.rs:84-93
+            uint32_t r = s_r0 + i, s = s_s0;
+            while (r >= a.per_sample) {
+                r -= a.per_sample;
+                s++;
+            }
+            const uint32_t py = r / a.width, px = r - py * a.width;
+            PcgRng rng;
+            rng.seed(a.seed, r, a.s_begin + s);
+            const float u = ((float)px + rng.next()) / (float)a.width;
+            const float v = ((float)py + rng.next()) / (float)a.height;
+            const Ray ray = camera_get_ray(sc.cam, u, v, rng);
+            P.o[pid] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.tm);
+            P.d[pid] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(WF_ALIVE));
+            P.b[pid] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(r));
+            uint2* st = reinterpret_cast<uint2*>(P.m + pid);
+            *st = make_uint2((uint32_t)rng.state, (uint32_t)(rng.state >> 32));
+            P.todo[n_surv + i] = (uint16_t)pid;  // consecutive pixels of a row sit next to each other
+        }
+        __syncthreads();
 #if RT_CTA_PROFILE
         { long long t = clock64(); if (tid == 0) { pf_phase[0] += t - pf_t; pf_phase[3]++; } pf_t = t; }
 #endif
 
         // ================================================================== A: traverse (one ray per lane)
         {
-            uint32_t* cnt = s_cnt[cur];
             CtaLane L;
             L.pid = CTA_NONE;
             L.ray.o = L.ray.d = mk3(0.0f, 0.0f, 0.0f);
@@ -410,40 +351,38 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
             L.xc.ro = L.ray;
             L.rng.state = 0;
             if (FLAT) {
-                // Tiny scenes: 32 entries per warp at a time (scattered and new paths alike), every lane walks the
-                // same primitive list — no refill, no stack, no divergence between node and leaf code.
+                // Tiny scenes: 32 todo entries per warp at a time (scattered and regenerated alike), every lane walks
+                // the same primitive list — no refill, no stack, no divergence between node and leaf code.
                 (void)stack;
-                const uint32_t n_todo = n_surv + n_cam;
+                const uint32_t n_todo = n_surv + n_regen;
                 for (;;) {
                     uint32_t base = 0;
                     if (lane == 0) base = atomicAdd(&s_next, 32u);
                     base = __shfl_sync(0xffffffffu, base, 0);
                     if (base >= n_todo) break;
-                    const uint32_t e = base + lane;
-                    bool active = e < n_todo;
+                    bool active = base + lane < n_todo;
                     if (active) {
-                        if (e < n_surv) cta_fetch<F, true>(P, P.todo[e], L);
-                        else cta_fetch_camera<F, true>(sc, a, P, P.cam[e - n_surv], L);
+                        cta_fetch<F>(P, P.todo[base + lane], L);
                         n_rays++;
                         active = L.ts.cur != TRAV_NONE;  // main.rs:39: a non-unit direction loses the path
                     }
                     flat_closest_hit<F, COUNT>(sc, L.ray, 1e-3f, L.ts, L.rng, false, active, &tc);
-                    if (e < n_todo) {
+                    if (base + lane < n_todo) {
                         L.ts.cur = TRAV_NONE;
-                        cta_retire<F>(P, L, cnt);
+                        cta_retire<F>(P, L, s_cnt);
                     }
                     __syncwarp();
                 }
             } else {
 #if RT_CTA_ONE_LOOP
-            // One instance of the traversal loop serves both lists (instruction-cache footprint): stage 0 = scattered
-            // rays, idle lanes refilled from the block's counter; stage 1 = new paths, a coherent chunk of 32
-            // neighbouring pixels at a time, run to completion.  `stage` is warp-uniform.
+            // One instance of the traversal loop serves both parts of the todo list (instruction-cache footprint):
+            // stage 0 = scattered rays, idle lanes refilled from the block's counter; stage 1 = camera rays, a
+            // coherent chunk of 32 neighbouring pixels at a time, run to completion.  `stage` is warp-uniform.
             bool more = n_surv != 0u;
             uint32_t stage = more ? 0u : 1u;
             for (;;) {
-                if (L.pid != CTA_NONE && L.ts.cur == TRAV_NONE) cta_retire<F>(P, L, cnt);
-                uint32_t idx = CTA_NONE;  // list entry this lane fetches now
+                if (L.pid != CTA_NONE && L.ts.cur == TRAV_NONE) cta_retire<F>(P, L, s_cnt);
+                uint32_t idx = CTA_NONE;  // todo entry this lane fetches now
                 if (stage == 0u) {
                     if (more) {
                         const uint32_t wm = __ballot_sync(0xffffffffu, L.pid == CTA_NONE);
@@ -462,13 +401,11 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
                     uint32_t base = 0;
                     if (lane == 0) base = atomicAdd(&s_nextp, 32u);
                     base = __shfl_sync(0xffffffffu, base, 0);
-                    if (base >= n_cam) break;
-                    if (base + lane < n_cam) {
-                        cta_fetch_camera<F, false>(sc, a, P, P.cam[base + lane], L);
-                        n_rays++;
-                    }
-                } else if (idx != CTA_NONE) {
-                    cta_fetch<F, false>(P, P.todo[idx], L);
+                    if (base >= n_regen) break;
+                    if (base + lane < n_regen) idx = n_surv + base + lane;
+                }
+                if (idx != CTA_NONE) {
+                    cta_fetch<F>(P, P.todo[idx], L);
                     n_rays++;
                 }
                 // ---- traverse until enough lanes are idle again (stage 0, while there is something to refill them
@@ -488,7 +425,7 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
             // ---- A2: scattered rays (incoherent): idle lanes are refilled from the block's counter
             bool more = n_surv != 0u;  // the todo list may still hold entries nobody has looked at (warp-uniform)
             for (;;) {
-                if (L.pid != CTA_NONE && L.ts.cur == TRAV_NONE) cta_retire<F>(P, L, cnt);
+                if (L.pid != CTA_NONE && L.ts.cur == TRAV_NONE) cta_retire<F>(P, L, s_cnt);
                 while (more) {
                     const uint32_t wm = __ballot_sync(0xffffffffu, L.pid == CTA_NONE);
                     if (wm == 0u) break;
@@ -498,7 +435,7 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
                     if (base + (uint32_t)__popc(wm) >= n_surv) more = false;
                     const uint32_t idx = base + (uint32_t)__popc(wm & ((1u << lane) - 1u));
                     if (L.pid == CTA_NONE && idx < n_surv) {
-                        cta_fetch<F, false>(P, P.todo[idx], L);
+                        cta_fetch<F>(P, P.todo[idx], L);
                         n_rays++;
                     }
                 }
@@ -515,15 +452,14 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
                     if (more && 32u - (uint32_t)__popc(busy) >= a.refill_idle) break;
                 }
             }
-            // ---- A1: new paths, 32 neighbouring pixels per warp: coherent, so the warp generates the camera rays and
-            //      runs them to completion
+            // ---- A1: camera rays, 32 neighbouring pixels per warp: coherent, so the warp runs them to completion
             for (;;) {
                 uint32_t base = 0;
                 if (lane == 0) base = atomicAdd(&s_nextp, 32u);
                 base = __shfl_sync(0xffffffffu, base, 0);
-                if (base >= n_cam) break;
-                if (base + lane < n_cam) {
-                    cta_fetch_camera<F, false>(sc, a, P, P.cam[base + lane], L);
+                if (base >= n_regen) break;
+                if (base + lane < n_regen) {
+                    cta_fetch<F>(P, P.todo[n_surv + base + lane], L);
                     n_rays++;
                     while (L.ts.cur != TRAV_NONE) {
                         while (!(L.ts.cur & LEAF_FLAG) && L.ts.cur != TRAV_NONE) node_visit<COUNT>(sc, L.rs, 1e-3f, L.ts, stack, &tc);
@@ -531,7 +467,7 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
                         leaf_visit<F, COUNT>(sc, L.ray, 1e-3f, L.ts, L.xc, L.rng, false, &tc);
                         L.ts.pop(stack);
                     }
-                    cta_retire<F>(P, L, cnt);
+                    cta_retire<F>(P, L, s_cnt);
                 }
                 __syncwarp();
             }
@@ -542,7 +478,6 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
         if (lane == 0) pf_work[0] += clock64() - pf_t;
 #endif
         __syncthreads();
-        if (tid == 0) s_next = s_nextp = 0u;  // (the traverse phase is over; the next one starts behind another barrier)
 #if RT_CTA_PROFILE
         { long long t = clock64(); if (tid == 0) pf_phase[1] += t - pf_t; pf_t = t; }
 #endif
@@ -551,11 +486,10 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
         {
             // Class ranges in a common index space, each padded to a warp multiple, the most expensive class
             // first; warps pull 32-entry chunks from a counter (longest-processing-time-first keeps the tail short).
-            const uint32_t* cnt = s_cnt[cur];
             uint32_t start[CLS_COUNT + 1];
             start[0] = 0u;
 #pragma unroll
-            for (int c = 0; c < CLS_COUNT; c++) start[c + 1] = start[c] + ((cnt[(c + 1) % CLS_COUNT] + 31u) & ~31u);  // 1..6, then 0
+            for (int c = 0; c < CLS_COUNT; c++) start[c + 1] = start[c] + ((s_cnt[(c + 1) % CLS_COUNT] + 31u) & ~31u);  // 1..6, then 0
             for (;;) {
                 uint32_t g = 0;
                 if (lane == 0) g = atomicAdd(&s_chunk, 32u);
@@ -570,49 +504,18 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
                 const uint32_t q = k == CLS_COUNT - 1 ? 0u : (uint32_t)k + 1u;  // queue of this chunk
                 const int cls = (int)((a.q_cls >> (4 * q)) & 0xfu);  // the class it shades as
                 const uint32_t idx = g - first + lane;
-                uint32_t pid = 0;
-                bool died = false;
-                if (idx < cnt[q]) {
-                    pid = P.list[q * N + idx];
-                    bool alive = false;
+                if (idx < s_cnt[q]) {
+                    const uint32_t pid = P.list[q * N + idx];
                     switch (cls) {
-                        case CLS_MISS: alive = cta_shade_item<F, CLS_MISS>(sc, a, P, pid, &s_ntodo[nxt], n_shade); break;
-                        case CLS_DIFFUSE_CONST: alive = cta_shade_item<F, CLS_DIFFUSE_CONST>(sc, a, P, pid, &s_ntodo[nxt], n_shade); break;
-                        case CLS_METAL: alive = cta_shade_item<F, CLS_METAL>(sc, a, P, pid, &s_ntodo[nxt], n_shade); break;
-                        case CLS_DIELECTRIC: alive = cta_shade_item<F, CLS_DIELECTRIC>(sc, a, P, pid, &s_ntodo[nxt], n_shade); break;
-                        case CLS_DIFFUSE_PERLIN: alive = cta_shade_item<F, CLS_DIFFUSE_PERLIN>(sc, a, P, pid, &s_ntodo[nxt], n_shade); break;
-                        case CLS_CLASSIC: alive = cta_shade_item<F, CLS_CLASSIC>(sc, a, P, pid, &s_ntodo[nxt], n_shade); break;
+                        case CLS_MISS: cta_shade_item<F, CLS_MISS>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
+                        case CLS_DIFFUSE_CONST: cta_shade_item<F, CLS_DIFFUSE_CONST>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
+                        case CLS_METAL: cta_shade_item<F, CLS_METAL>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
+                        case CLS_DIELECTRIC: cta_shade_item<F, CLS_DIELECTRIC>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
+                        case CLS_DIFFUSE_PERLIN: cta_shade_item<F, CLS_DIFFUSE_PERLIN>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
+                        case CLS_CLASSIC: cta_shade_item<F, CLS_CLASSIC>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade); break;
                         default:
-                            if ((MASK >> CLS_PBR) & 1u) alive = cta_shade_item<F, CLS_PBR>(sc, a, P, pid, &s_ntodo[nxt], n_shade);
+                            if ((MASK >> CLS_PBR) & 1u) cta_shade_item<F, CLS_PBR>(sc, a, P, pid, &s_ndead, &s_ntodo, n_shade);
                             break;
-                    }
-                    died = !alive;
-                }
-                // ---- the slots whose path ended start a new one: path indices from the block's reservation (one
-                //      shared-memory atomic per warp), the slot onto the camera list; the ray itself is generated by
-                //      the warp that fetches it (cta_fetch_camera)
-                const uint32_t dm = __ballot_sync(0xffffffffu, died);
-                if (dm != 0u) {
-                    const uint32_t n_died = (uint32_t)__popc(dm);
-                    uint32_t j0 = 0, pos0 = 0;
-                    if (lane == 0) {
-                        j0 = atomicAdd(&s_alloc, n_died);
-                        const uint32_t total = s_seg.len_a + s_seg.len_b;
-                        const uint32_t n_new = j0 >= total ? 0u : min(n_died, total - j0);
-                        if (n_new) pos0 = atomicAdd(&s_ncam[nxt], n_new);
-                    }
-                    j0 = __shfl_sync(0xffffffffu, j0, 0);
-                    pos0 = __shfl_sync(0xffffffffu, pos0, 0);
-                    const uint32_t rank = (uint32_t)__popc(dm & ((1u << lane) - 1u));
-                    if (died) {
-                        P.d[pid].w = __uint_as_float(0u);
-                        if (j0 + rank < s_seg.len_a + s_seg.len_b) {
-                            uint32_t r, s;
-                            path_of(j0 + rank, r, s);
-                            P.b[pid] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(r));
-                            P.o[pid].x = __uint_as_float(s);
-                            P.cam[pos0 + rank] = (uint16_t)pid;
-                        }
                     }
                 }
                 __syncwarp();
@@ -620,12 +523,11 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
         }
 #if RT_CTA_PROFILE
         if (lane == 0) pf_work[1] += clock64() - pf_t;
+#endif
+        __syncthreads();
+#if RT_CTA_PROFILE
         { long long t = clock64(); if (tid == 0) pf_phase[2] += t - pf_t; pf_t = t; }
 #endif
-    }
-    if (COUNT && tid == 0) {  // the queue lengths of the last iteration
-#pragma unroll
-        for (int c = 0; c < 8; c++) cls_total[c] += s_cnt[0][c] + s_cnt[1][c];
     }
 #if RT_CTA_PROFILE
     if (tid == 0) {
