@@ -3,7 +3,8 @@
 The GPU uses its own per-path RNG streams, so the comparison is statistical.  Tolerances, stated:
   * |mean luminance difference| <= 0.5 %  (BASELINE.json north_star)  at >= 1024 spp on small frames
     (looser bound 3 sigma-style for the quick low-spp cases);
-  * per-channel RMSE(gpu, oracle) <= 1.25 x RMSE(oracle seed A, oracle seed B)  (the noise floor).
+  * per-channel RMSE(gpu, oracle) <= 1.25 x RMSE(oracle seed A, oracle seed B)  (the noise floor), the RMSE taken as
+    the median over five GPU seeds (see test_render_matches_oracle).
 """
 import os
 
@@ -74,9 +75,18 @@ def test_render_matches_oracle(rtlib, oracle, name, w, h, spp, tol, mode):
     # mean-luminance check above stays unclipped.  NaN pixels (the reference has no NaN filter, main.rs:98-105)
     # are excluded and their count is compared instead.
     cap = float(np.nanpercentile(a, 99.5))
-    ca, cb, ci = np.clip(a, 0, cap), np.clip(b, 0, cap), np.clip(img, 0, cap)
+    ca, cb = np.clip(a, 0, cap), np.clip(b, 0, cap)
     noise = np.sqrt(np.nanmean((ca - cb) ** 2, axis=(0, 1)))
-    rmse = np.sqrt(np.nanmean((ci - ca) ** 2, axis=(0, 1)))
+    # The RMSE of ONE render against the oracle is itself a heavy-tailed statistic on the firefly-prone scenes: over
+    # 12 GPU seeds pbr_ibl at this size gives rmse/noise = 1.06-1.10 on average with a spread of ~0.1, and single seeds
+    # reach 1.28 (and 1.51 with the generator of round 1) — profiles/r02_experiments/rng_output_ab_vs_oracle.log.  The
+    # stated bound (1.25 x the oracle's own seed-to-seed RMSE) is therefore applied to the MEDIAN over five independent
+    # GPU renders: one unlucky seed cannot fail it, a systematic error moves all five.
+    rmses = [np.sqrt(np.nanmean((np.clip(img, 0, cap) - ca) ** 2, axis=(0, 1)))]
+    for seed in (1, 2, 3, 4):
+        other, _ = scene.render(w, h, spp, mode=mode, seed=seed)
+        rmses.append(np.sqrt(np.nanmean((np.clip(other, 0, cap) - ca) ** 2, axis=(0, 1))))
+    rmse = np.median(np.stack(rmses), axis=0)
     nan_gpu, nan_cpu = int(np.isnan(img).any(-1).sum()), int(np.isnan(a).any(-1).sum())
     assert abs(nan_gpu - nan_cpu) <= 3 + 0.5 * max(nan_gpu, nan_cpu), (nan_gpu, nan_cpu)
     rpp_gpu = st.rays / st.paths
