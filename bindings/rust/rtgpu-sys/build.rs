@@ -41,7 +41,7 @@ fn main() {
         run(Command::new("g++").args(host_flags).arg("-c").arg(csrc.join(format!("{s}.cpp"))).arg("-o").arg(&o));
         objs.push(o);
     }
-    for s in ["rtgpu", "rt_comm", "gpu_bvh"] {
+    for s in ["rtgpu", "rt_comm", "rt_static", "gpu_bvh"] {
         let o = obj(s);
         run(Command::new(&nvcc).args(cuda_flags).arg("-c").arg(csrc.join(format!("{s}.cu"))).arg("-o").arg(&o).current_dir(&csrc));
         objs.push(o);

@@ -66,6 +66,7 @@ pub const RT_RENDER_COUNTERS: u32 = 1;
 pub const RT_RENDER_RUSSIAN_ROULETTE: u32 = 2;
 pub const RT_RENDER_COSINE_SAMPLING: u32 = 4;
 pub const RT_COMM_UNIQUE_ID_BYTES: usize = 128;
+pub const RT_STATIC_MAX_RAYS: u32 = 65536;
 
 #[repr(C)]
 #[derive(Clone, Copy, Default)]
@@ -247,6 +248,7 @@ extern "C" {
     pub fn rt_flat_shade_queues(desc: *const RtFlatScene, mat_queue: *mut u8, q_class: *mut u32, q_order: *mut u32) -> c_int;
     pub fn rt_closest_hit(scene: *mut RtScene, o_xyz: *const f32, d_xyz: *const f32, times: *const f32, n: usize, t_min: f32, t_max: f32, out: *mut RtHit) -> c_int;
     pub fn rt_closest_hit_device(scene: *mut RtScene, o_xyz: *const f32, d_xyz: *const f32, times: *const f32, n: usize, t_min: f32, t_max: f32, out: *mut RtHit, cuda_stream: *mut c_void) -> c_int;
+    pub fn rt_closest_hit_static(scene: *mut RtScene, o_xyz: *const f32, d_xyz: *const f32, times: *const f32, n: usize, t_min: f32, t_max: f32, out: *mut RtHit, out_n_hits: *mut u64) -> c_int;
     pub fn rt_camera_get_rays(cam: *const RtCamera, uv: *const f32, n: usize, o_xyz: *mut f32, d_xyz: *mut f32) -> c_int;
     pub fn rt_render_device(scene: *mut RtScene, params: *const RtRenderParams, accum_sum_rgb: *mut f32, cuda_stream: *mut c_void, stats: *mut RtStats) -> c_int;
     pub fn rt_render(scene: *mut RtScene, params: *const RtRenderParams, out_rgb_mean: *mut f32, stats: *mut RtStats) -> c_int;

@@ -287,6 +287,19 @@ int rt_closest_hit_device(RtScene* scene, const float* o_xyz, const float* d_xyz
                           const float* times, size_t n, float t_min, float t_max, RtHit* out,
                           void* cuda_stream);
 
+/* Same query as rt_closest_hit (HOST buffers in and out, same records), allocating NOTHING: the device staging of
+ * the rays and of the hit records lives in a static device array inside the library (4.5 MiB, held by every GPU that
+ * loads the library until the process exits) instead of leased / cudaMalloc'ed scratch.
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * At most RT_STATIC_MAX_RAYS rays per call: a larger n is rejected with RT_ERR_ARG (split the batch, or call
+ * rt_closest_hit).  *out_n_hits (optional) = rays that hit something.  Synchronous on the scene's own stream.
+ * Every call on a device shares the one array: calls that overlap on the same GPU (other host threads, other scenes
+ * on that device) race — serialise them. */
+#define RT_STATIC_MAX_RAYS 65536u
+int rt_closest_hit_static(RtScene* scene, const float* o_xyz, const float* d_xyz, const float* times,
+                          size_t n, float t_min, float t_max, RtHit* out, uint64_t* out_n_hits);
+
 /* Camera rays for pixel centres or explicit (u,v): replaces Camera::get_ray (src/camera.rs:40-46)
  * on the host side so that GPU and oracle are fed bit-identical rays. uv is n*2 floats. */
 int rt_camera_get_rays(const RtCamera* cam, const float* uv, size_t n, float* o_xyz, float* d_xyz);

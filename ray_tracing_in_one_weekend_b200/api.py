@@ -17,6 +17,7 @@ LIB_PATH = os.environ.get("RTGPU_LIB") or os.path.join(HERE, "librtgpu.so")  # R
 TEST_LIB_PATH = os.path.join(HERE, "librtgpu_test.so")  # product objects + rt_test_* hooks (tests only)
 RT_ERR_ARG, RT_ERR_CUDA, RT_ERR_IO, RT_ERR_UNSUPPORTED, RT_ERR_NCCL = -1, -2, -3, -4, -5
 COMM_UNIQUE_ID_BYTES = 128
+STATIC_MAX_RAYS = 65536
 ASSET_DIR = os.path.join(REPO, "assets")
 
 RT_ABI_VERSION = 2
@@ -134,7 +135,7 @@ EXPORTED_SYMBOLS = [
     "rt_flat_shade_queues", "rt_last_error", "rt_host_scene_build", "rt_host_scene_flat", "rt_host_scene_destroy",
     "rt_flat_validate", "rt_release_cached_memory", "rt_partition_samples", "rt_comm_unique_id", "rt_comm_create",
     "rt_comm_create_all", "rt_comm_info", "rt_comm_destroy", "rt_render_reduce", "rt_render_reduce_device",
-    "rt_scene_kernel_times",
+    "rt_scene_kernel_times", "rt_closest_hit_static",
 ]
 
 _lib: Optional[C.CDLL] = None
@@ -155,6 +156,7 @@ def _declare(lib: C.CDLL) -> None:
     lib.rt_release_cached_memory.argtypes = []
     lib.rt_release_cached_memory.restype = None
     lib.rt_closest_hit.argtypes = [vp, vp, vp, vp, sz, C.c_float, C.c_float, vp]
+    lib.rt_closest_hit_static.argtypes = [vp, vp, vp, vp, sz, C.c_float, C.c_float, vp, C.POINTER(C.c_uint64)]
     lib.rt_closest_hit_device.argtypes = [vp, vp, vp, vp, sz, C.c_float, C.c_float, vp, vp]
     lib.rt_camera_get_rays.argtypes = [C.POINTER(RtCamera), vp, sz, vp, vp]
     lib.rt_render_device.argtypes = [vp, C.POINTER(RtRenderParams), vp, vp, C.POINTER(RtStats)]
@@ -368,6 +370,21 @@ class Scene:
         _check(self._lib.rt_closest_hit(self._h, _ptr(o), _ptr(d), _ptr(times), n, C.c_float(t_min), C.c_float(t_max),
                                         _ptr(out)), self._lib)
         return out
+
+    def closest_hit_static(self, o: np.ndarray, d: np.ndarray, t_min: float = 1e-3, t_max: float = 3.4028234663852886e38,
+                           times: Optional[np.ndarray] = None):
+        """rt_closest_hit_static: the same query with its device staging in the library's static array (no
+        allocation; at most STATIC_MAX_RAYS rays).  Returns (HIT_DTYPE array, number of rays that hit)."""
+        o = np.ascontiguousarray(o, dtype=np.float32)
+        d = np.ascontiguousarray(d, dtype=np.float32)
+        n = o.shape[0]
+        if times is not None:
+            times = np.ascontiguousarray(times, dtype=np.float32)
+        out = np.zeros(n, dtype=HIT_DTYPE)
+        n_hits = C.c_uint64()
+        _check(self._lib.rt_closest_hit_static(self._h, _ptr(o), _ptr(d), _ptr(times), n, C.c_float(t_min), C.c_float(t_max),
+                                               _ptr(out), C.byref(n_hits)), self._lib)
+        return out, n_hits.value
 
     def make_params(self, width: int, height: int, spp: int, *, sample_begin: int = 0,
                     sample_end: Optional[int] = None, spp_total: Optional[int] = None, max_depth: int = 50,

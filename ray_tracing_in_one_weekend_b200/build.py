@@ -21,7 +21,7 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 CXX = os.environ.get("CXX", "g++")
 
 HOST_SRCS = ["scene_api.cpp", "demo_scene.cpp", "bvh_build.cpp", "png_writer.cpp"]
-CUDA_SRCS = ["rtgpu.cu", "rt_comm.cu", "gpu_bvh.cu"]
+CUDA_SRCS = ["rtgpu.cu", "rt_comm.cu", "rt_static.cu", "gpu_bvh.cu"]
 TEST_SRCS = ["test_hooks.cu"]
 CTA_FEATURE_SETS = [0, 4, 8, 9, 11, 15]  # cta_inst.cu is compiled once per set (kernels_cta.cuh)
 CTA_NO_PBR_SETS = [0, 4]  # ... and once more without the pbr.rs shading class for the sphere-only sets
