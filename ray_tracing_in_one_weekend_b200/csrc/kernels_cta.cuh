@@ -189,8 +189,8 @@ struct CtaLane {
 };
 
 // Load the ray of pool slot `idx` into the lane and set its traversal up (main.rs:39-44).
-template <uint32_t F>
-RT_DEV void cta_fetch(const CtaPool& P, uint32_t idx, CtaLane& L) {
+template <uint32_t F, bool COUNT = false, bool FLAT = false>
+RT_DEV void cta_fetch(const DeviceScene& sc, const CtaPool& P, uint32_t idx, CtaLane& L, TravCounters* tc) {
     const float4 rd = P.d[idx], ro = P.o[idx];
     L.pid = idx;
     L.ray.o = mk3(ro.x, ro.y, ro.z);
@@ -207,6 +207,7 @@ RT_DEV void cta_fetch(const CtaPool& P, uint32_t idx, CtaLane& L) {
     }
     if (vec3a_near_one(L.ray.d)) {
         L.rs.init(L.ray);
+        if (!FLAT) giants_test<COUNT>(sc, L.ray, 1e-3f, L.ts, tc);  // (the flat loop walks every world primitive itself)
     } else {
         // main.rs:39: a non-unit direction loses the path; it retires as a miss with zero throughput
         P.b[idx] = make_float4(0.0f, 0.0f, 0.0f, P.b[idx].w);
@@ -362,7 +363,7 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
                     if (base >= n_todo) break;
                     bool active = base + lane < n_todo;
                     if (active) {
-                        cta_fetch<F>(P, P.todo[base + lane], L);
+                        cta_fetch<F, COUNT, true>(sc, P, P.todo[base + lane], L, &tc);
                         n_rays++;
                         active = L.ts.cur != TRAV_NONE;  // main.rs:39: a non-unit direction loses the path
                     }
@@ -405,7 +406,7 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
                     if (base + lane < n_regen) idx = n_surv + base + lane;
                 }
                 if (idx != CTA_NONE) {
-                    cta_fetch<F>(P, P.todo[idx], L);
+                    cta_fetch<F, COUNT>(sc, P, P.todo[idx], L, &tc);
                     n_rays++;
                 }
                 // ---- traverse until enough lanes are idle again (stage 0, while there is something to refill them
@@ -435,7 +436,7 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
                     if (base + (uint32_t)__popc(wm) >= n_surv) more = false;
                     const uint32_t idx = base + (uint32_t)__popc(wm & ((1u << lane) - 1u));
                     if (L.pid == CTA_NONE && idx < n_surv) {
-                        cta_fetch<F>(P, P.todo[idx], L);
+                        cta_fetch<F, COUNT>(sc, P, P.todo[idx], L, &tc);
                         n_rays++;
                     }
                 }
@@ -459,7 +460,7 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
                 base = __shfl_sync(0xffffffffu, base, 0);
                 if (base >= n_regen) break;
                 if (base + lane < n_regen) {
-                    cta_fetch<F>(P, P.todo[n_surv + base + lane], L);
+                    cta_fetch<F, COUNT>(sc, P, P.todo[n_surv + base + lane], L, &tc);
                     n_rays++;
                     while (L.ts.cur != TRAV_NONE) {
                         while (!(L.ts.cur & LEAF_FLAG) && L.ts.cur != TRAV_NONE) node_visit<COUNT>(sc, L.rs, 1e-3f, L.ts, stack, &tc);

@@ -466,6 +466,37 @@ int rt_scene_create_ex(const RtFlatScene* desc, int device, uint32_t flags, RtSc
     s->knob_flat = dev_knob("RT_CTA_FLAT", -1);
     stage("stream/events/attrs");
 
+    // "Giant" primitives (rt_device.cuh giants_test): untransformed static spheres whose extent exceeds 64 x the median
+    // extent of the world primitives, at most two, in scenes of more than 64 world primitives (smaller scenes take the
+    // flat loop or gain nothing).  The builders see a copy of the description in which they are flagged boundary-only,
+    // i.e. not part of the world; the kernels test them once per ray before the tree.
+    std::vector<uint32_t> giants;
+    std::vector<RtPrim> prims_for_bvh;
+    RtFlatScene bvh_desc = *desc;
+    uint32_t n_world_total = 0;
+    {
+        std::vector<float> ext;
+        for (uint32_t i = 0; i < desc->n_prims; i++) {
+            const RtPrim& p = desc->prims[i];
+            if (p.flags & RT_PRIM_FLAG_BOUNDARY_ONLY) continue;
+            n_world_total++;
+            if (p.kind == RT_PRIM_SPHERE || p.kind == RT_PRIM_MOVING_SPHERE) ext.push_back(2.0f * p.g[3]);
+            else if (p.kind != RT_PRIM_MEDIUM) ext.push_back(std::fmax(std::fmax(std::fabs(p.g[3] - p.g[0]), std::fabs(p.g[4] - p.g[1])), std::fabs(p.g[5] - p.g[2])));
+        }
+        if (n_world_total > 64u && !ext.empty() && dev_knob("RT_GIANTS", 1) != 0) {
+            std::nth_element(ext.begin(), ext.begin() + ext.size() / 2, ext.end());
+            const float median = ext[ext.size() / 2];
+            for (uint32_t i = 0; i < desc->n_prims && giants.size() < 2; i++) {
+                const RtPrim& p = desc->prims[i];
+                if (!(p.flags & RT_PRIM_FLAG_BOUNDARY_ONLY) && p.kind == RT_PRIM_SPHERE && p.xform == 0 && 2.0f * p.g[3] > 64.0f * median) giants.push_back(i);
+            }
+        }
+        if (!giants.empty()) {
+            prims_for_bvh.assign(desc->prims, desc->prims + desc->n_prims);
+            for (uint32_t g : giants) prims_for_bvh[g].flags |= RT_PRIM_FLAG_BOUNDARY_ONLY;
+            bvh_desc.prims = prims_for_bvh.data();
+        }
+    }
     // acceleration structure: host SAH builder (default) or the GPU LBVH builder
     BvhBuildResult bvh;
     uint32_t builder = 0;
@@ -474,7 +505,7 @@ int rt_scene_create_ex(const RtFlatScene* desc, int device, uint32_t flags, RtSc
     if (flags & RT_SCENE_GPU_BVH) {
         GpuBvhResult g;
         std::string err;
-        if (!gpu_build_bvh4(*desc, s->stream, g, err)) return fail(RT_ERR_CUDA, "GPU BVH build: " + err);
+        if (!gpu_build_bvh4(bvh_desc, s->stream, g, err)) return fail(RT_ERR_CUDA, "GPU BVH build: " + err);
         if (g.max_depth * 3u + 4u <= (uint32_t)STACK_SIZE) {
             s->gpu_nodes = g.nodes;
             bvh.leaf_order = std::move(g.leaf_order);
@@ -489,7 +520,7 @@ int rt_scene_create_ex(const RtFlatScene* desc, int device, uint32_t flags, RtSc
     }
     if (builder == 0) {
         try {
-            build_bvh4(*desc, (uint32_t)dev_knob("RT_LEAF_MAX", 1), bvh);
+            build_bvh4(bvh_desc, (uint32_t)dev_knob("RT_LEAF_MAX", 1), bvh);
         } catch (const std::exception& e) {
             return fail(RT_ERR_ARG, e.what());
         }
@@ -499,7 +530,10 @@ int rt_scene_create_ex(const RtFlatScene* desc, int device, uint32_t flags, RtSc
     stage("bvh build");
 
     // device primitive array: world primitives in BVH leaf order, then boundary-only primitives in flat order
+    // ... with the giants between the two
     std::vector<uint32_t> order = bvh.leaf_order;
+    const uint32_t giant_first = (uint32_t)order.size();
+    for (uint32_t g : giants) order.push_back(g);
     for (uint32_t i = 0; i < desc->n_prims; i++)
         if (desc->prims[i].flags & RT_PRIM_FLAG_BOUNDARY_ONLY) order.push_back(i);
     std::vector<uint32_t> flat_to_dev(desc->n_prims, 0xffffffffu);
@@ -685,10 +719,12 @@ int rt_scene_create_ex(const RtFlatScene* desc, int device, uint32_t flags, RtSc
     const RtCamera& c = desc->camera;
     auto v3 = [](const float* p) { return V3f{p[0], p[1], p[2]}; };
     s->ds.cam = DevCamera{v3(c.origin), v3(c.horizontal), v3(c.vertical), v3(c.lower_left_corner), v3(c.u), v3(c.v), c.lens_radius, c.time0, c.time1};
-    s->ds.n_world_prims = bvh.n_world_prims;
+    s->ds.n_world_prims = n_world_total;  // (the flat loop's count; scenes that take it have no giants)
     s->ds.n_prims = (uint32_t)prims.size();
     s->ds.has_media = has_media ? 1u : 0u;
-    s->n_world_prims = bvh.n_world_prims;
+    s->ds.giant_first = giant_first;
+    s->ds.n_giants = (uint32_t)giants.size();
+    s->n_world_prims = n_world_total;
     for (uint32_t i = 0; i < desc->n_prims; i++) {
         const RtPrim& p = desc->prims[i];
         if (p.xform != 0) s->features |= F_XFORM;
@@ -697,7 +733,7 @@ int rt_scene_create_ex(const RtFlatScene* desc, int device, uint32_t flags, RtSc
         if (p.kind == RT_PRIM_XYRECT || p.kind == RT_PRIM_XZRECT || p.kind == RT_PRIM_YZRECT) s->features |= F_RECT;
     }
     s->camera = c;
-    s->bvh = RtBvhInfo{(uint32_t)bvh.nodes.size(), bvh.n_world_prims, bvh.max_depth, bvh.max_leaf_prims, bvh.sah_cost, (uint32_t)sizeof(BvhNode4), builder, build_ms,
+    s->bvh = RtBvhInfo{(uint32_t)bvh.nodes.size(), n_world_total, bvh.max_depth, bvh.max_leaf_prims, bvh.sah_cost, (uint32_t)sizeof(BvhNode4), builder, build_ms,
                        (uint64_t)total};
     CU_TRY(cudaStreamSynchronize(s->stream));  // the staging buffer goes back to the cache when this function returns
     stage("upload + sync");
