@@ -65,6 +65,7 @@ pub const RT_SCENE_GPU_BVH: u32 = 1;
 pub const RT_RENDER_COUNTERS: u32 = 1;
 pub const RT_RENDER_RUSSIAN_ROULETTE: u32 = 2;
 pub const RT_RENDER_COSINE_SAMPLING: u32 = 4;
+pub const RT_RENDER_LOBE_SAMPLING: u32 = 8;
 pub const RT_COMM_UNIQUE_ID_BYTES: usize = 128;
 pub const RT_STATIC_MAX_RAYS: u32 = 65536;
 

@@ -331,6 +331,12 @@ typedef struct RtRenderParams {
                                         material draw the scattered direction cosine-weighted (pdf cos/pi) instead
                                         of uniformly on the hemisphere (src/material.rs:52-59, src/pbr.rs) and
                                         re-weight by 1/(2 cos).  Same expectation, less variance. */
+#define RT_RENDER_LOBE_SAMPLING 8u /* OPT-IN estimator, outside the parity contract (takes precedence over
+                                      RT_RENDER_COSINE_SAMPLING): every pbr.rs material draws the scattered direction
+                                      from a 50/50 mixture of cosine-weighted and GGX-half-vector sampling of its own
+                                      lobe width instead of uniformly on the hemisphere (src/pbr.rs:19,53,163,201,235,
+                                      289,317) and re-weights by (1/2pi)/pdf; Lambert draws cosine-weighted.  Same
+                                      expectation, bounded weights on the sharp lobes (no fireflies / NaN pixels). */
 #define RT_RENDER_RUSSIAN_ROULETTE 2u /* OPT-IN estimator, outside the parity contract: after every scatter the
                                          path survives with probability min(max_element(attenuation), 1) and its
                                          throughput is divided by it (the reference has this commented out,

@@ -34,6 +34,7 @@ MODE_AUTO, MODE_MEGAKERNEL, MODE_CTA_WAVEFRONT = 0, 1, 3  # (2 was the global-me
 RENDER_COUNTERS = 1
 RENDER_RUSSIAN_ROULETTE = 2
 RENDER_COSINE_SAMPLING = 4
+RENDER_LOBE_SAMPLING = 8
 SCENE_GPU_BVH = 1
 
 

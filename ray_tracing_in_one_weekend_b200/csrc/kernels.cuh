@@ -122,7 +122,7 @@ __global__ void __launch_bounds__(MEGA_THREADS) k_render_mega(DeviceScene sc, Re
                         HitRec rec = fill_hit<F>(sc, ray, h.prim, h.t, (m.reserved & 1u) != 0u);
                         V3f emitted, att;
                         Ray scattered;
-                        bool ok = shade(sc, m, ray, rec, rng, emitted, att, scattered, (a.max_depth & DEPTH_COS_FLAG) != 0u);
+                        bool ok = shade(sc, m, ray, rec, rng, emitted, att, scattered, sampling_of(a.max_depth));
                         sum = sum + beta * emitted;  // main.rs:47
                         if (ok && (a.max_depth & DEPTH_RR_FLAG)) ok = russian_roulette(att, rng);
                         if (ok) {                    // main.rs:48-54

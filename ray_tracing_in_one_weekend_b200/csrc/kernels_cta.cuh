@@ -148,7 +148,7 @@ RT_DEV void cta_shade_item(const DeviceScene& sc, const CtaArgs& a, const CtaPoo
         HitRec rec = fill_hit<F>(sc, ray, mm.w, __uint_as_float(mm.z), want_uv);
         V3f emitted, att;
         Ray scattered;
-        bool ok = shade_cls<CLS>(sc, m, ray, rec, rng, emitted, att, scattered, (a.max_depth & DEPTH_COS_FLAG) != 0u, P.perlin);
+        bool ok = shade_cls<CLS>(sc, m, ray, rec, rng, emitted, att, scattered, sampling_of(a.max_depth), P.perlin);
         if (CLS == CLS_CLASSIC) add = beta * emitted;  // main.rs:47 (only Emission emits, material.rs:26-28)
         if (ok && (a.max_depth & DEPTH_RR_FLAG)) ok = russian_roulette(att, rng);
         if (ok) {                                      // main.rs:48-54

@@ -876,7 +876,7 @@ int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* c
     if (rp->width == 0 || rp->height == 0 || rp->sample_end < rp->sample_begin) return fail(RT_ERR_ARG, "bad render params");
     if (rp->mode != RT_MODE_AUTO && rp->mode != RT_MODE_MEGAKERNEL && rp->mode != RT_MODE_CTA_WAVEFRONT) return fail(RT_ERR_ARG, "bad render mode");
     if (rp->max_depth > DEPTH_MASK) return fail(RT_ERR_ARG, "max_depth too large");
-    if (rp->flags & ~(RT_RENDER_COUNTERS | RT_RENDER_RUSSIAN_ROULETTE | RT_RENDER_COSINE_SAMPLING)) return fail(RT_ERR_ARG, "unknown render flag");
+    if (rp->flags & ~(RT_RENDER_COUNTERS | RT_RENDER_RUSSIAN_ROULETTE | RT_RENDER_COSINE_SAMPLING | RT_RENDER_LOBE_SAMPLING)) return fail(RT_ERR_ARG, "unknown render flag");
     if ((uint64_t)rp->width * rp->height >= (1ull << 31)) return fail(RT_ERR_ARG, "image too large");
     auto w0 = std::chrono::steady_clock::now();
     CU_TRY(cudaSetDevice(s->device));
@@ -885,7 +885,8 @@ int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* c
     const bool count = (rp->flags & RT_RENDER_COUNTERS) != 0;
     const uint32_t n_samples = rp->sample_end - rp->sample_begin;
     const uint32_t depth_word = rp->max_depth | ((rp->flags & RT_RENDER_RUSSIAN_ROULETTE) ? DEPTH_RR_FLAG : 0u) |
-                                ((rp->flags & RT_RENDER_COSINE_SAMPLING) ? DEPTH_COS_FLAG : 0u);
+                                ((rp->flags & RT_RENDER_COSINE_SAMPLING) ? DEPTH_COS_FLAG : 0u) |
+                                ((rp->flags & RT_RENDER_LOBE_SAMPLING) ? DEPTH_LOBE_FLAG : 0u);
     uint32_t launches = 0;
     if (n_samples) {
         CU_TRY(cudaMemsetAsync(s->scratch, 0, 18 * sizeof(unsigned long long), st));  // statistics + both work counters
