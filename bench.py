@@ -75,6 +75,18 @@ def scene_note(name):
     return SCENE_NOTES.get(name, "extension scene")
 
 
+def workload_config(scene, w, h, spp, world, l2_note):
+    """The `config` block — identical for both arms (`--impl ours` / `--impl reference`)."""
+    return {"workload": f"{scene} ({scene_note(scene)}) {w}x{h}, {spp} spp per GPU ({spp * world} spp frame), depth {MAX_DEPTH}, "
+                        "samples of every pixel partitioned over the GPUs + one sum-reduce per frame",
+            "scene": scene, "width": w, "height": h, "spp_per_gpu": spp, "spp_total": spp * world, "max_depth": MAX_DEPTH,
+            "parallelism": f"spp-split x{world}", "l2": l2_note}
+
+
+L2_NOTE = ("256 MiB buffer written between timed steps (L2 flush) on the GPU arm; the scene working set is L1/L2-resident by design; "
+           "the CPU arm has no device cache to flush")
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -197,9 +209,9 @@ def run_reference(args, rank):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total_s / max(1, len(vals)),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "mrays_s": sum(v["rays"] for v in vals) / total_s / 1e6,
-        "config": {"workload": f"{args.scene} ({scene_note(args.scene)}) {args.width}x{args.height}, depth {MAX_DEPTH}; "
-                               "each step = a bounded strided column sample at 16 spp",
-                   "scene": args.scene, "width": args.width, "height": args.height, "max_depth": MAX_DEPTH},
+        "config": workload_config(args.scene, args.width, args.height, args.spp, max(1, args.gpus), L2_NOTE),
+        "details": {"timed": "each step = a bounded strided column sample of that frame at 16 spp on the host cores (CPU throughput in "
+                             "Mpaths/s does not depend on spp); rank 0 only"},
         "cpu_baseline": {"value": value, "unit": "Mpaths/s", "cores": last["threads"], "kind": "port",
                          "sample": last["sample"]},
         "e2e": {"value": value, "unit": "Mpaths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -436,14 +448,10 @@ def run_ours(args, rank, world, local_rank):
             "warmup": warm, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "mrays_s": mrays, "rays_per_path": rays_per_step / paths_per_step,
-            "config": {"workload": f"{args.scene} ({scene_note(args.scene)}) {W}x{H}, {SPP} spp per GPU "
-                                   f"({spp_total} spp frame), depth {MAX_DEPTH}, spp-partitioned + one ncclReduce inside librtgpu.so "
-                                   "(rt_render_reduce_device)",
-                       "scene": args.scene, "width": W, "height": H, "spp_per_gpu": SPP, "spp_total": spp_total,
-                       "max_depth": MAX_DEPTH, "mode": int(st.mode_used), "parallelism": f"spp-split x{world}",
-                       "l2": "256 MiB buffer written between timed steps (L2 flush); scene working set is L1/L2-resident by design",
-                       "bvh": {"nodes": info.n_nodes, "node_bytes": info.node_bytes, "depth": info.max_depth,
-                               "max_leaf": info.max_leaf_prims, "sah": info.sah_cost}},
+            "config": workload_config(args.scene, W, H, SPP, world, L2_NOTE),
+            "details": {"mode": int(st.mode_used), "frame_call": "rt_render_reduce_device (spp partition + ncclReduce inside librtgpu.so)",
+                        "bvh": {"nodes": info.n_nodes, "node_bytes": info.node_bytes, "depth": info.max_depth,
+                                "max_leaf": info.max_leaf_prims, "sah": info.sah_cost}},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": int(W * H * 12), "steps": len(e2e_ms), "ms_median": e2e_med,
