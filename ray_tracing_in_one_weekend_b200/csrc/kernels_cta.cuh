@@ -99,7 +99,7 @@ struct CtaArgs {
 };
 
 // Bytes of dynamic shared memory for a pool of n paths.
-constexpr size_t CTA_PERLIN_BYTES = 256 * 16 + 768;
+constexpr size_t CTA_PERLIN_BYTES = 256 * 16 + 768 * 2;  // 256 gradients + 768 permutation PAIRS (rt_device.cuh PerlinShared)
 inline size_t cta_smem_bytes(uint32_t n, bool perlin) {
     return (((size_t)n * (64 + 2 * (CLS_COUNT + 2)) + 15) & ~(size_t)15) + (perlin ? CTA_PERLIN_BYTES : 0);
 }
@@ -255,8 +255,12 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
     P.perlin = nullptr;
     if (a.stage_perlin) {
         float4* dst = reinterpret_cast<float4*>(reinterpret_cast<char*>(cta_smem) + (((size_t)N * (64 + 2 * (CLS_COUNT + 2)) + 15) & ~(size_t)15));
-        for (uint32_t i = tid; i < 256u + 48u; i += CTA_THREADS)  // 256 gradients + 768 permutation bytes as 48 float4
-            dst[i] = i < 256u ? __ldg(sc.perlin_grad_lin + i) : __ldg(reinterpret_cast<const float4*>(sc.perlin_perm) + (i - 256u));
+        for (uint32_t i = tid; i < 256u; i += CTA_THREADS) dst[i] = __ldg(sc.perlin_grad_lin + i);
+        uint16_t* pairs = reinterpret_cast<uint16_t*>(dst + 256);
+        for (uint32_t i = tid; i < 768u; i += CTA_THREADS) {
+            const uint32_t axis = i >> 8, k = i & 255u;
+            pairs[i] = (uint16_t)(__ldg(sc.perlin_perm + axis * 256u + k) | (__ldg(sc.perlin_perm + axis * 256u + ((k + 1u) & 255u)) << 8));
+        }
         P.perlin = dst;
     }
 
