@@ -313,3 +313,69 @@ def test_k15_perlin_table_known_answer(oracle, rtlib):
         perms.append(list(p))
     assert [perms[0][:8], perms[1][:8], perms[2][:8]] == [K15_PERM_X, K15_PERM_Y, K15_PERM_Z]
     assert sorted(perms[2]) == list(range(256))
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# K16: ConstantMedium::hit (hitable.rs:536-579) by hand.  Medium of density 0.5 (neg_inv_density = -2) bounded by the
+# unit sphere at the origin; unit-length ray directions, so distances along the ray are t.
+#   ray from (-3,0,0) along +x: boundary roots t = 2 and t = 4 (oc = (-3,0,0): half_b = -3, c = 8, disc = 1), the second
+#   query starts at 2 + 1e-4 and finds 4.  xi = 0.5: hit_dist = -2 ln 0.5 = 1.3862944 <= (4 - 2) -> t = 3.3862944,
+#   p = (0.3862944, 0, 0), norm = (1,0,0), front_face = true, ONE draw.  xi = 0.25: hit_dist = 2.7725887 > 2 -> miss,
+#   one draw.  A ray that misses the sphere: no hit, NO draw.  Origin inside (0,0,0): roots -1 and 1; t1 = -1 is clamped
+#   to t_min = 0.001, t2 = 1; xi = 0.9: hit_dist = -2 ln 0.9 = 0.21072103 <= 0.999 -> t = 0.21172103.
+#   [t_min, t_max] = [0.001, 3]: t2 clamped to 3, xi = 0.5: 1.3862944 > (3 - 2) -> miss.  [2.5, inf): t1 clamped to 2.5,
+#   xi = 0.5: 1.3862944 <= 1.5 -> t = 3.8862944.  t_max = 1.5 (< t1): t2 clamped to 1.5 <= t1 -> miss before any draw.
+def _medium_flat(api):
+    prims = (api.RtPrim * 2)()
+    prims[0].kind, prims[0].mat, prims[0].flags = api.PRIM_SPHERE, 0, api.PRIM_FLAG_BOUNDARY_ONLY
+    prims[0].g[0:4] = [0.0, 0.0, 0.0, 1.0]
+    prims[1].kind, prims[1].mat, prims[1].aux0, prims[1].aux1 = api.PRIM_MEDIUM, 1, 0, 1
+    prims[1].g[0] = -2.0
+    tex = (api.RtTexture * 1)()
+    tex[0].kind = api.TEX_CONSTANT
+    tex[0].p[0:3] = [0.5, 0.5, 0.5]
+    mats = (api.RtMaterial * 2)()
+    mats[0].kind, mats[0].tex0 = api.MAT_DIFFUSE, 0
+    mats[1].kind, mats[1].tex0 = api.MAT_ISOTROPIC, 0
+    chains = (api.RtXformChain * 1)()
+    fs = api.RtFlatScene()
+    fs.abi_version = api.RT_ABI_VERSION
+    fs.n_prims, fs.prims = 2, prims
+    fs.n_xform_chains, fs.xform_chains = 1, chains
+    fs.n_materials, fs.materials = 2, mats
+    fs.n_textures, fs.textures = 1, tex
+    return fs, (prims, tex, mats, chains)
+
+
+def test_k16_constant_medium_known_answers(oracle, rtlib):
+    api = rtlib.api
+    fs, keep = _medium_flat(api)
+    rtlib.flat_validate(C.pointer(fs))  # the hand-built description is well formed
+    sc = oracle.OracleScene.from_flat(C.pointer(fs))
+    INF = np.float32(np.inf)
+    f32 = np.float32
+
+    def t_of(t1, xi):  # the reference's binary32 steps: hit_dist = neg_inv_density * ln(xi); t = t1 + hit_dist / |d|
+        return f32(t1) + f32(-2.0) * np.log(f32(xi)) / f32(1.0)
+
+    cases = [  # origin, direction, t_min, t_max, xi -> hit, draws, t
+        ((-3, 0, 0), (1, 0, 0), 1e-3, INF, 0.5, 1, 1, t_of(2.0, 0.5)),
+        ((-3, 0, 0), (1, 0, 0), 1e-3, INF, 0.25, 0, 1, None),
+        ((-3, 2, 0), (1, 0, 0), 1e-3, INF, 0.5, 0, 0, None),
+        ((0, 0, 0), (1, 0, 0), 1e-3, INF, 0.9, 1, 1, t_of(1e-3, 0.9)),
+        ((-3, 0, 0), (1, 0, 0), 1e-3, 3.0, 0.5, 0, 1, None),
+        ((-3, 0, 0), (1, 0, 0), 2.5, INF, 0.5, 1, 1, t_of(2.5, 0.5)),
+        ((-3, 0, 0), (1, 0, 0), 1e-3, 1.5, 0.5, 0, 0, None),
+    ]
+    rays = np.array([list(o) + list(d) for o, d, *_ in cases], np.float32)
+    tmm = np.array([[c[2], c[3]] for c in cases], np.float32)
+    xi = np.array([c[4] for c in cases], np.float32)
+    got = sc.medium_cases(1, rays, tmm, xi)
+    for k, (o, d, _, _, _, hit, draws, t) in enumerate(cases):
+        assert int(got[k, 0]) == hit and int(got[k, 2]) == draws, (k, got[k])
+        if hit:
+            np.testing.assert_allclose(got[k, 1], t, rtol=2.5e-7)  # (numpy's float32 log vs glibc logf: <= 1 ulp)
+            np.testing.assert_allclose(got[k, 3:6], np.array(o, np.float64) + t * np.array(d, np.float64), rtol=0, atol=5e-7)
+            assert got[k, 6:10].tolist() == [1.0, 0.0, 0.0, 1.0]  # norm (1,0,0), front_face = true (hitable.rs:570-571)
+    np.testing.assert_allclose(got[0, 1], 3.3862944, rtol=2e-7)
+    np.testing.assert_allclose(got[3, 1], 0.21172103, rtol=5e-7)
