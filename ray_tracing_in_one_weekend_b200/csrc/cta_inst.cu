@@ -19,8 +19,9 @@
 #endif
 
 namespace rtb {
-void* RT_CTA_ENTRY(bool count, int* threads) {
+void* RT_CTA_ENTRY(bool count, int* threads, int* pool_paths) {
     if (threads) *threads = CTA_THREADS;
+    if (pool_paths) *pool_paths = (int)CTA_POOL_PATHS;
     return count ? (void*)k_render_cta<(uint32_t)RT_CTA_F, true, (uint32_t)RT_CTA_CLS_MASK, (RT_CTA_FLAT) != 0>
                  : (void*)k_render_cta<(uint32_t)RT_CTA_F, false, (uint32_t)RT_CTA_CLS_MASK, (RT_CTA_FLAT) != 0>;
 }

@@ -55,6 +55,19 @@ namespace rtb {
 #ifndef RT_CTA_MIN_BLOCKS
 #define RT_CTA_MIN_BLOCKS 2  // register cap 85 (80 used): fits traversal and the common shading classes
 #endif
+// Paths per block pool, a COMPILE-TIME constant of every build (exported next to the block size): the pool's arrays
+// sit at multiples of N in shared memory, and with N in a register every path-state access carried its own uniform
+// multiply/shift to find them (144 instructions of the spheres-only kernel, all in the per-ray fetch / retire / shade
+// prologues).  1152 = 3 paths per thread; the sets that may stage the Perlin table (no media) give one warp's worth of
+// paths to it so that two blocks stay inside the 196 KB carve-out (rtgpu.cu cta_plan).  0 = run-time (CtaArgs.n_paths,
+// development sweeps: tools/build_variant.py -DRT_CTA_POOL_PATHS=0 + RT_CTA_PATHS).
+#ifndef RT_CTA_POOL_PATHS
+#if defined(RT_CTA_F) && ((RT_CTA_F) & 2)
+#define RT_CTA_POOL_PATHS 1152
+#else
+#define RT_CTA_POOL_PATHS 1120
+#endif
+#endif
 // Traverse phase: 1 = scattered rays and camera rays share ONE instance of the traversal loop.  The media sets inline
 // a medium test into every leaf visit: one instance instead of two takes 2 100 instructions (34 KB) out of the
 // kernel and its spills from 56 to 8 B — cornell_box +6.6 %, final_scene +4.9 % (the instruction cache was the
@@ -74,12 +87,16 @@ namespace rtb {
 #ifndef RT_CTA_CLS_MASK
 #define RT_CTA_CLS_MASK 0x7fu
 #endif
+#ifndef RT_CTA_DECODE_TREE
+#define RT_CTA_DECODE_TREE 1  // shade phase: chunk -> queue by a compare tree (0: counting compares + select chain)
+#endif
 #ifndef RT_CTA_PROFILE
 #define RT_CTA_PROFILE 0  // development: phase / work cycle counters into stats[8..13] (class_counts of RtStats)
 #endif
 constexpr int CTA_THREADS = RT_CTA_THREADS;
 constexpr int CTA_WARPS = CTA_THREADS / 32;
 constexpr int CTA_MIN_BLOCKS = RT_CTA_MIN_BLOCKS;
+constexpr uint32_t CTA_POOL_PATHS = RT_CTA_POOL_PATHS;
 constexpr uint32_t CTA_NONE = 0xffffffffu;
 
 struct CtaArgs {
@@ -89,8 +106,10 @@ struct CtaArgs {
     unsigned long long total_paths;    // width * height * n_samples
     uint32_t width, height, s_begin, max_depth;
     uint32_t per_sample;   // width * height (< 2^31)
-    uint32_t n_paths;      // N: paths per block pool (multiple of 32, <= 4096)
+    uint32_t n_paths;      // N: paths per block pool (multiple of 32, <= 4096); builds with CTA_POOL_PATHS != 0 ignore it
     uint32_t refill_idle;  // a warp retires/refills once this many of its lanes are idle
+    uint32_t refill_camera;  // ... the same once the refill has reached the camera rays (unified_todo)
+    uint32_t unified_todo;   // 1: lane refill runs through the camera-ray part of the todo list as well
     uint32_t stage_perlin;  // 1: Perlin table 0 is copied into shared memory (scenes with Diffuse(PerlinTex))
     // Shade queues (rtgpu.cu assign_shade_queues): queue 0 = misses, queue q = bits 9..11 of the hit primitive's
     // record, numbered most expensive class first.  4 bits per queue: the shading class (CLS_*) it runs.
@@ -178,6 +197,26 @@ RT_DEV void cta_shade_item(const DeviceScene& sc, const CtaArgs& a, const CtaPoo
     }
 }
 
+// Lane 0 takes `n` entries from a block-wide shared-memory counter and every lane gets the old value.  ptxas rewrites
+// every shared-memory atomic whose ADDRESS it can prove warp-uniform into its aggregation sequence (vote, find-leader,
+// two popcounts, lane masks, shuffle: 17 instructions), also when ONE lane executes it and also through inline PTX:
+// three such sites ran 135 M times per 64-spp frame of the cover scene, 2 % of the kernel's warp instructions
+// (profiles/r02_cta_ncu_headline.md: device_atomic_functions.hpp:112 rows at 1.0 threads per instruction).  Adding
+// threadIdx.y (always 0: blocks are one-dimensional) makes the address thread-dependent as far as ptxas can tell, and
+// the atomic stays the single ATOMS.ADD it is.
+#ifndef RT_CTA_PLAIN_TAKE
+#define RT_CTA_PLAIN_TAKE 1
+#endif
+RT_DEV uint32_t warp_take(uint32_t* counter, uint32_t n, uint32_t lane) {
+    uint32_t old = 0;
+#if RT_CTA_PLAIN_TAKE
+    if (lane == 0) old = atomicAdd(counter + threadIdx.y, n);
+#else
+    if (lane == 0) old = atomicAdd(counter, n);
+#endif
+    return __shfl_sync(0xffffffffu, old, 0);
+}
+
 // Traversal registers of one lane.
 struct CtaLane {
     uint32_t pid;
@@ -242,7 +281,7 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
     __shared__ uint32_t s_nsurv, s_nregen, s_r0, s_s0;
 
     const uint32_t tid = threadIdx.x, lane = tid & 31u;
-    const uint32_t N = a.n_paths;
+    const uint32_t N = CTA_POOL_PATHS ? CTA_POOL_PATHS : a.n_paths;
     CtaPool P;
     P.o = cta_smem;
     P.d = P.o + N;
@@ -361,9 +400,7 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
                 (void)stack;
                 const uint32_t n_todo = n_surv + n_regen;
                 for (;;) {
-                    uint32_t base = 0;
-                    if (lane == 0) base = atomicAdd(&s_next, 32u);
-                    base = __shfl_sync(0xffffffffu, base, 0);
+                    const uint32_t base = warp_take(&s_next, 32u, lane);
                     if (base >= n_todo) break;
                     bool active = base + lane < n_todo;
                     if (active) {
@@ -379,12 +416,22 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
                     __syncwarp();
                 }
             } else {
+            // The todo list holds the scattered rays [0, n_surv) and behind them the camera rays of the regenerated
+            // paths.  Entries [0, n_list) are handed out with lane refill, the rest 32 neighbouring pixels at a time
+            // to whole warps that run them to completion.  n_list = n_surv keeps the camera rays coherent (large
+            // trees: their node fetches stay broadcasts); n_list = everything ("unified", small trees) tops the lanes a
+            // warp has left when the scattered part runs dry up with camera rays instead of letting them finish on
+            // their own — the tail is 30 % of the scattered part's lane slots at 56 scattered rays per warp and
+            // iteration (tools/bvh_sim.cpp).  The host decides per scene (rtgpu.cu cta_plan).
+            const uint32_t n_list = a.unified_todo ? n_surv + n_regen : n_surv;
+            const uint32_t n_rest = n_surv + n_regen - n_list;
 #if RT_CTA_ONE_LOOP
             // One instance of the traversal loop serves both parts of the todo list (instruction-cache footprint):
             // stage 0 = scattered rays, idle lanes refilled from the block's counter; stage 1 = camera rays, a
             // coherent chunk of 32 neighbouring pixels at a time, run to completion.  `stage` is warp-uniform.
-            bool more = n_surv != 0u;
+            bool more = n_list != 0u;
             uint32_t stage = more ? 0u : 1u;
+            uint32_t thr = a.refill_idle;
             for (;;) {
                 if (L.pid != CTA_NONE && L.ts.cur == TRAV_NONE) cta_retire<F>(P, L, s_cnt);
                 uint32_t idx = CTA_NONE;  // todo entry this lane fetches now
@@ -392,22 +439,19 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
                     if (more) {
                         const uint32_t wm = __ballot_sync(0xffffffffu, L.pid == CTA_NONE);
                         if (wm != 0u) {
-                            uint32_t base = 0;
-                            if (lane == 0) base = atomicAdd(&s_next, (uint32_t)__popc(wm));
-                            base = __shfl_sync(0xffffffffu, base, 0);
-                            if (base + (uint32_t)__popc(wm) >= n_surv) more = false;
+                            const uint32_t base = warp_take(&s_next, (uint32_t)__popc(wm), lane);
+                            if (base + (uint32_t)__popc(wm) >= n_list) more = false;
+                            if (base + (uint32_t)__popc(wm) >= n_surv) thr = a.refill_camera;
                             const uint32_t i = base + (uint32_t)__popc(wm & ((1u << lane) - 1u));
-                            if (L.pid == CTA_NONE && i < n_surv) idx = i;
+                            if (L.pid == CTA_NONE && i < n_list) idx = i;
                         }
                     }
                     if (!__any_sync(0xffffffffu, L.pid != CTA_NONE || idx != CTA_NONE)) stage = 1u;  // scattered part drained
                 }
                 if (stage == 1u) {  // every lane is idle here
-                    uint32_t base = 0;
-                    if (lane == 0) base = atomicAdd(&s_nextp, 32u);
-                    base = __shfl_sync(0xffffffffu, base, 0);
-                    if (base >= n_regen) break;
-                    if (base + lane < n_regen) idx = n_surv + base + lane;
+                    const uint32_t base = warp_take(&s_nextp, 32u, lane);
+                    if (base >= n_rest) break;
+                    if (base + lane < n_rest) idx = n_list + base + lane;
                 }
                 if (idx != CTA_NONE) {
                     cta_fetch<F, COUNT>(sc, P, P.todo[idx], L, &tc);
@@ -423,23 +467,23 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
                     }
                     const uint32_t busy = __ballot_sync(0xffffffffu, L.ts.cur != TRAV_NONE);
                     if (busy == 0u) break;
-                    if (stage == 0u && more && 32u - (uint32_t)__popc(busy) >= a.refill_idle) break;
+                    if (stage == 0u && more && 32u - (uint32_t)__popc(busy) >= thr) break;
                 }
             }
 #else
             // ---- A2: scattered rays (incoherent): idle lanes are refilled from the block's counter
-            bool more = n_surv != 0u;  // the todo list may still hold entries nobody has looked at (warp-uniform)
+            bool more = n_list != 0u;  // the todo list may still hold entries nobody has looked at (warp-uniform)
+            uint32_t thr = a.refill_idle;
             for (;;) {
                 if (L.pid != CTA_NONE && L.ts.cur == TRAV_NONE) cta_retire<F>(P, L, s_cnt);
                 while (more) {
                     const uint32_t wm = __ballot_sync(0xffffffffu, L.pid == CTA_NONE);
                     if (wm == 0u) break;
-                    uint32_t base = 0;
-                    if (lane == 0) base = atomicAdd(&s_next, (uint32_t)__popc(wm));
-                    base = __shfl_sync(0xffffffffu, base, 0);
-                    if (base + (uint32_t)__popc(wm) >= n_surv) more = false;
+                    const uint32_t base = warp_take(&s_next, (uint32_t)__popc(wm), lane);
+                    if (base + (uint32_t)__popc(wm) >= n_list) more = false;
+                    if (base + (uint32_t)__popc(wm) >= n_surv) thr = a.refill_camera;  // (the camera part of a unified list)
                     const uint32_t idx = base + (uint32_t)__popc(wm & ((1u << lane) - 1u));
-                    if (L.pid == CTA_NONE && idx < n_surv) {
+                    if (L.pid == CTA_NONE && idx < n_list) {
                         cta_fetch<F, COUNT>(sc, P, P.todo[idx], L, &tc);
                         n_rays++;
                     }
@@ -454,17 +498,15 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
                     }
                     const uint32_t busy = __ballot_sync(0xffffffffu, L.ts.cur != TRAV_NONE);
                     if (busy == 0u) break;
-                    if (more && 32u - (uint32_t)__popc(busy) >= a.refill_idle) break;
+                    if (more && 32u - (uint32_t)__popc(busy) >= thr) break;
                 }
             }
             // ---- A1: camera rays, 32 neighbouring pixels per warp: coherent, so the warp runs them to completion
             for (;;) {
-                uint32_t base = 0;
-                if (lane == 0) base = atomicAdd(&s_nextp, 32u);
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (base >= n_regen) break;
-                if (base + lane < n_regen) {
-                    cta_fetch<F, COUNT>(sc, P, P.todo[n_surv + base + lane], L, &tc);
+                const uint32_t base = warp_take(&s_nextp, 32u, lane);
+                if (base >= n_rest) break;
+                if (base + lane < n_rest) {
+                    cta_fetch<F, COUNT>(sc, P, P.todo[n_list + base + lane], L, &tc);
                     n_rays++;
                     while (L.ts.cur != TRAV_NONE) {
                         while (!(L.ts.cur & LEAF_FLAG) && L.ts.cur != TRAV_NONE) node_visit<COUNT>(sc, L.rs, 1e-3f, L.ts, stack, &tc);
@@ -496,16 +538,31 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
 #pragma unroll
             for (int c = 0; c < CLS_COUNT; c++) start[c + 1] = start[c] + ((s_cnt[(c + 1) % CLS_COUNT] + 31u) & ~31u);  // 1..6, then 0
             for (;;) {
-                uint32_t g = 0;
-                if (lane == 0) g = atomicAdd(&s_chunk, 32u);
-                g = __shfl_sync(0xffffffffu, g, 0);
+                const uint32_t g = warp_take(&s_chunk, 32u, lane);
                 if (g >= start[CLS_COUNT]) break;
+#if RT_CTA_DECODE_TREE
+                // range k of the chunk (g is warp-uniform): three uniform compares down a tree instead of six + six selects
+                static_assert(CLS_COUNT == 7, "the decode tree below is written for seven queues");
+                uint32_t k, first;
+                if (g < start[3]) {
+                    if (g < start[1]) { k = 0u; first = 0u; }
+                    else if (g < start[2]) { k = 1u; first = start[1]; }
+                    else { k = 2u; first = start[2]; }
+                } else if (g < start[5]) {
+                    if (g < start[4]) { k = 3u; first = start[3]; }
+                    else { k = 4u; first = start[4]; }
+                } else {
+                    if (g < start[6]) { k = 5u; first = start[5]; }
+                    else { k = 6u; first = start[6]; }
+                }
+#else
                 int k = 0;
 #pragma unroll
                 for (int c = 1; c < CLS_COUNT; c++) k += g >= start[c] ? 1 : 0;
                 uint32_t first = 0;
 #pragma unroll
                 for (int c = 1; c < CLS_COUNT; c++) first = k == c ? start[c] : first;
+#endif
                 const uint32_t q = k == CLS_COUNT - 1 ? 0u : (uint32_t)k + 1u;  // queue of this chunk
                 const int cls = (int)((a.q_cls >> (4 * q)) & 0xfu);  // the class it shades as
                 const uint32_t idx = g - first + lane;
@@ -568,43 +625,43 @@ __global__ void __launch_bounds__(CTA_THREADS, CTA_MIN_BLOCKS) k_render_cta(Devi
 
 // Host-side entry points, one translation unit per instantiated feature set (cta_inst.cu, -DRT_CTA_F=<F>).
 // Feature sets built: 0 (spheres only), F_MOTION, F_RECT, F_RECT|F_XFORM, F_RECT|F_XFORM|F_MEDIA, F_ALL.
-void* cta_kernel_f0(bool count, int* threads);  // *threads = block size the kernel was built for
-void* cta_kernel_f4(bool count, int* threads);
-void* cta_kernel_f8(bool count, int* threads);
-void* cta_kernel_f9(bool count, int* threads);
-void* cta_kernel_f11(bool count, int* threads);
-void* cta_kernel_f15(bool count, int* threads);
-void* cta_kernel_f0_m3f(bool count, int* threads);  // the same without the pbr.rs shading class
-void* cta_kernel_f4_m3f(bool count, int* threads);
-void* cta_kernel_f0_flat(bool count, int* threads);  // FLAT builds (tiny scenes): spheres; + rects; + transforms; + media
-void* cta_kernel_f8_flat(bool count, int* threads);
-void* cta_kernel_f9_flat(bool count, int* threads);
-void* cta_kernel_f11_flat(bool count, int* threads);
+void* cta_kernel_f0(bool count, int* threads, int* pool_paths);  // *threads = block size the kernel was built for
+void* cta_kernel_f4(bool count, int* threads, int* pool_paths);
+void* cta_kernel_f8(bool count, int* threads, int* pool_paths);
+void* cta_kernel_f9(bool count, int* threads, int* pool_paths);
+void* cta_kernel_f11(bool count, int* threads, int* pool_paths);
+void* cta_kernel_f15(bool count, int* threads, int* pool_paths);
+void* cta_kernel_f0_m3f(bool count, int* threads, int* pool_paths);  // the same without the pbr.rs shading class
+void* cta_kernel_f4_m3f(bool count, int* threads, int* pool_paths);
+void* cta_kernel_f0_flat(bool count, int* threads, int* pool_paths);  // FLAT builds (tiny scenes): spheres; + rects; + transforms; + media
+void* cta_kernel_f8_flat(bool count, int* threads, int* pool_paths);
+void* cta_kernel_f9_flat(bool count, int* threads, int* pool_paths);
+void* cta_kernel_f11_flat(bool count, int* threads, int* pool_paths);
 
 // The kernel of the smallest built feature set that covers `features`.
-inline void* cta_kernel_for(uint32_t features, uint32_t class_mask, bool count, bool flat, uint32_t* built, int* threads) {
-    struct E { uint32_t f; void* (*fn)(bool, int*); };
+inline void* cta_kernel_for(uint32_t features, uint32_t class_mask, bool count, bool flat, uint32_t* built, int* threads, int* pool_paths = nullptr) {
+    struct E { uint32_t f; void* (*fn)(bool, int*, int*); };
     if (flat) {
         const E flat_table[] = {{0u, cta_kernel_f0_flat}, {8u, cta_kernel_f8_flat}, {9u, cta_kernel_f9_flat}, {11u, cta_kernel_f11_flat}};
         for (const E& e : flat_table)
             if ((features & ~e.f) == 0u) {
                 if (built) *built = e.f;
-                return e.fn(count, threads);
+                return e.fn(count, threads, pool_paths);
             }
     }
     if (!((class_mask >> CLS_PBR) & 1u)) {  // no pbr.rs material in the scene
-        if (features == 0u) { if (built) *built = 0u; return cta_kernel_f0_m3f(count, threads); }
-        if (features == 4u) { if (built) *built = 4u; return cta_kernel_f4_m3f(count, threads); }
+        if (features == 0u) { if (built) *built = 0u; return cta_kernel_f0_m3f(count, threads, pool_paths); }
+        if (features == 4u) { if (built) *built = 4u; return cta_kernel_f4_m3f(count, threads, pool_paths); }
     }
     const E table[] = {{0u, cta_kernel_f0}, {4u, cta_kernel_f4}, {8u, cta_kernel_f8}, {9u, cta_kernel_f9},
                        {11u, cta_kernel_f11}, {15u, cta_kernel_f15}};
     for (const E& e : table)
         if ((features & ~e.f) == 0u) {
             if (built) *built = e.f;
-            return e.fn(count, threads);
+            return e.fn(count, threads, pool_paths);
         }
     if (built) *built = 15u;
-    return cta_kernel_f15(count, threads);
+    return cta_kernel_f15(count, threads, pool_paths);
 }
 
 }  // namespace rtb

@@ -87,7 +87,7 @@ struct CtaPlan {
     int threads = 0;
     int blocks_per_sm = 0;
     size_t smem = 0;
-    uint32_t n_paths = 0, refill_idle = 0, stage_perlin = 0;
+    uint32_t n_paths = 0, refill_idle = 0, refill_camera = 0, unified_todo = 0, stage_perlin = 0;
     bool flat = false;  // the warp-uniform primitive loop (tiny scenes) instead of the BVH traversal
 };
 
@@ -130,7 +130,7 @@ struct RtScene {
     int mega_blocks_per_sm[2] = {0, 0};
     // development knobs (RT_DEV_KNOBS builds read them from the environment ONCE, in rt_scene_create)
     int knob_mode = 0, knob_paths = 0, knob_refill = 8, knob_blocks = 64, knob_carveout = -1, knob_full_kernel = 0,
-        knob_units_per_warp = 24, knob_flat = -1;
+        knob_units_per_warp = 24, knob_flat = -1, knob_unified = -1, knob_refill_camera = 24;
 
     ~RtScene();
 };

@@ -458,6 +458,8 @@ int rt_scene_create_ex(const RtFlatScene* desc, int device, uint32_t flags, RtSc
     CU_TRY(cudaDeviceGetAttribute(&pitch_align, cudaDevAttrTexturePitchAlignment, device));
     s->knob_mode = dev_knob("RT_DEFAULT_MODE", RT_MODE_CTA_WAVEFRONT);
     s->knob_paths = dev_knob("RT_CTA_PATHS", 0);
+    s->knob_unified = dev_knob("RT_CTA_UNIFIED", -1);
+    s->knob_refill_camera = dev_knob("RT_CTA_REFILL_CAMERA", 24);
     s->knob_refill = dev_knob("RT_CTA_REFILL", 8);
     s->knob_blocks = dev_knob("RT_CTA_BLOCKS", 64);
     s->knob_carveout = dev_knob("RT_CTA_CARVEOUT", -1);
@@ -840,21 +842,36 @@ int rt_camera_get_rays(const RtCamera* cam, const float* uv, size_t n, float* o_
 }  // extern "C"
 
 // Launch plan of the CTA-wavefront kernel for this scene, resolved on first use and kept in the handle.
+// Scenes without media whose tree has at most this many 128-byte nodes (1 MB) trace scattered and camera rays from ONE
+// refilled list (kernels_cta.cuh, traverse phase).  Measured on B200 at 1080p, separate -> unified with a camera-part
+// threshold of 24 idle lanes (profiles/r02_experiments/unified_todo_list_per_scene.log): cover scene (282 nodes) +2.4 %,
+// textured +4.1 %, cover_defocus +2.2 %, cover_4k_motion +0.7 %; cover_100k_motion (tens of thousands of nodes: the
+// coherent camera warps' node fetches are broadcasts) -1.7 %, final_scene (media set, one-loop kernel) -1.4 %.
+static constexpr uint32_t UNIFIED_TODO_MAX_NODES = 8192;
+
 static int cta_plan(RtScene* s, bool count, const CtaPlan** out) {
     CtaPlan& p = s->cta_plan[count ? 1 : 0];
     if (!p.fn) {
-        // Pool size: 1152 paths (92 KB per block, 196 KB carve-out, ~60 KB of L1) = 3 paths per thread of a 384-thread
-        // block, 3.6 per thread of the 320-thread blocks of the media kernels (measured: 1152 > 1120 > 992 > 864).
-        // Scenes with Diffuse(PerlinTex) (and no media) stage Perlin table 0 in shared memory (4.75 KB): one warp's
-        // worth of paths less keeps the block inside the same carve-out (+2..8 % on those scenes).
+        // Pool size: a compile-time constant of every kernel build (kernels_cta.cuh RT_CTA_POOL_PATHS) — 1152 paths
+        // (92 KB per block, 196 KB carve-out, ~60 KB of L1) = 3.6 paths per thread of the 320-thread media builds, and
+        // one warp's worth less (1120) for every build that may stage Perlin table 0 in shared memory (5.5 KB; scenes
+        // with Diffuse(PerlinTex) and no media), so that two blocks stay inside the same carve-out with it (measured
+        // in round 1: 1152 > 1120 > 992 > 864, staging +2..8 % on those scenes).  Builds with a run-time pool size
+        // (development, RT_CTA_POOL_PATHS=0) take it from the RT_CTA_PATHS knob.
         const bool media = (s->features & F_MEDIA) != 0;
         p.stage_perlin = !media && (s->class_mask >> CLS_DIFFUSE_PERLIN & 1u) && s->ds.n_perlin > 0 ? 1u : 0u;
         // Tiny scenes (<= 32 world primitives, no moving spheres): the warp-uniform primitive loop replaces the BVH
         p.flat = (s->features & F_MOTION) == 0u && s->n_world_prims <= (uint32_t)(s->knob_flat >= 0 ? s->knob_flat : 32);
-        void* fn = cta_kernel_for(s->features, s->knob_full_kernel ? 0x7fu : s->class_mask, count, p.flat, nullptr, &p.threads);
+        int built_paths = 0;
+        void* fn = cta_kernel_for(s->features, s->knob_full_kernel ? 0x7fu : s->class_mask, count, p.flat, nullptr, &p.threads, &built_paths);
         const int dflt_paths = p.stage_perlin ? 1120 : 1152;
-        p.n_paths = (uint32_t)std::max(32, std::min(4096, s->knob_paths > 0 ? s->knob_paths : dflt_paths)) & ~31u;
+        p.n_paths = built_paths > 0 ? (uint32_t)built_paths
+                                    : (uint32_t)std::max(32, std::min(4096, s->knob_paths > 0 ? s->knob_paths : dflt_paths)) & ~31u;
         p.refill_idle = (uint32_t)std::max(1, std::min(32, s->knob_refill));
+        p.refill_camera = (uint32_t)std::max(1, std::min(32, s->knob_refill_camera));
+        // One refilled list for scattered and camera rays (small trees, no media); otherwise the camera rays keep their
+        // coherent warps (UNIFIED_TODO_MAX_NODES above).
+        p.unified_todo = s->knob_unified >= 0 ? (uint32_t)(s->knob_unified != 0) : (!media && s->bvh.n_nodes <= UNIFIED_TODO_MAX_NODES ? 1u : 0u);
         p.smem = cta_smem_bytes(p.n_paths, p.stage_perlin != 0u);
         CU_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.smem));
         if (s->knob_carveout >= 0)  // development: shared-memory carve-out in percent (the rest is L1)
@@ -911,6 +928,8 @@ int rt_render_device(RtScene* s, const RtRenderParams* rp, float* accum, void* c
             a.stage_perlin = plan->stage_perlin;
             a.n_paths = plan->n_paths;
             a.refill_idle = plan->refill_idle;
+            a.refill_camera = plan->refill_camera;
+            a.unified_todo = plan->unified_todo;
             a.seed = rp->seed;
             a.q_cls = s->q_cls;
             // never more blocks than there are pools of work
