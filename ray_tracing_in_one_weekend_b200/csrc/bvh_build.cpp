@@ -151,7 +151,10 @@ struct Builder {
         for (uint32_t i = begin; i < end; i++) cb.grow_pt(&cen[3 * idx[i]]);
         int best_axis = -1;
         float best_cost = INFINITY, best_pos = 0.0f;
-        constexpr int NB = 32;
+#ifndef RT_BVH_BINS
+#define RT_BVH_BINS 32
+#endif
+        constexpr int NB = RT_BVH_BINS;
         if (!force_median) {
             for (int a = 0; a < 3; a++) {
                 float lo = cb.lo[a], hi = cb.hi[a];
@@ -239,7 +242,11 @@ struct Builder {
             for (size_t k = 0; k < kids.size(); k++) {
                 uint32_t n = kids[k].end - kids[k].begin;
                 if (n < 2) continue;
+#ifdef RT_BVH_PICK_AREA
+                float score = kids[k].box.area();
+#else
                 float score = kids[k].box.area() * (float)n;
+#endif
                 if (score > best) {
                     best = score;
                     pick = (int)k;

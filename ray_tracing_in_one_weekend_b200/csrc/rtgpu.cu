@@ -409,13 +409,17 @@ int rt_partition_samples(uint32_t sample_begin, uint32_t sample_end, int n_ranks
 }
 
 int rt_scene_create(const RtFlatScene* desc, int device, RtScene** out) {
-    // builder policy (results are identical either way): scenes of >= 32768 world primitives are built on the
-    // device (same traversal speed as the SAH tree at that size, ~20x faster build), smaller ones on the host
+    // Builder policy (results are identical either way): the host SAH tree up to 262 144 world primitives, the device
+    // LBVH from there on.  The SAH tree traverses faster — cover_100k_motion (99 860 spheres) renders 1 172 against 977
+    // Mpaths/s at 1080p, cover_4k_motion 2 792 against 2 380 (B200, tools/builder_ab.py) — and builds in 0.3 s at
+    // 100 k primitives, which a frame of a few samples per pixel at that size already repays; a caller that rebuilds
+    // its scene every frame asks for the device builder with rt_scene_create_ex(RT_SCENE_GPU_BVH).
+    constexpr uint32_t AUTO_GPU_BVH_MIN_PRIMS = 262144u;
     uint32_t flags = 0;
-    if (desc && desc->prims && desc->n_prims >= 32768u) {
+    if (desc && desc->prims && desc->n_prims >= AUTO_GPU_BVH_MIN_PRIMS) {
         uint32_t world = 0;
         for (uint32_t i = 0; i < desc->n_prims; i++) world += (desc->prims[i].flags & RT_PRIM_FLAG_BOUNDARY_ONLY) ? 0u : 1u;
-        if (world >= 32768u) flags = RT_SCENE_GPU_BVH;
+        if (world >= AUTO_GPU_BVH_MIN_PRIMS) flags = RT_SCENE_GPU_BVH;
     }
     const int forced = dev_knob("RT_SCENE_FLAGS", -1);
     if (forced >= 0) flags = (uint32_t)forced;

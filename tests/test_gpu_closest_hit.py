@@ -20,7 +20,7 @@ SCENES = [
     ("final_scene", 200, 200),        # 1000 transformed spheres + 400 boxes (coplanar shared faces -> exact ties)
     ("pbr_ibl", 240, 135),
     ("cover_4k_motion", 240, 160),    # moving spheres, per-ray time
-    ("cover_100k_motion", 64, 36),    # cfg5: 99 860 spheres (GPU-built LBVH by default); small batch, the list oracle is O(n) per ray
+    ("cover_100k_motion", 64, 36),    # cfg5: 99 860 spheres (host SAH tree by default, LBVH on request: test_gpu_bvh_build.py); small batch, the list oracle is O(n) per ray
 ]
 
 

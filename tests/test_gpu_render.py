@@ -32,7 +32,7 @@ CASES = [
     ("pbr_ibl", 96, 54, 512, 0.006),
     ("cover_defocus", 96, 64, 256, 0.008),
     ("cover_4k_motion", 96, 64, 256, 0.008),
-    ("cover_100k_motion", 96, 54, 256, 0.008),    # cfg5: 99 860 spheres, device-built LBVH, motion kernel
+    ("cover_100k_motion", 96, 54, 256, 0.008),    # cfg5: 99 860 spheres, motion kernel
     ("smoke_instances", 48, 48, 1024, 0.02),      # media under Translate / RotateY wrappers (hitable.rs:404-520 over 523-588)
 ]
 

@@ -41,6 +41,12 @@ static V in_sphere() {
     }
 }
 
+struct WNode {  // node of width <= 16 for the model (collapsed from the builder's 4-wide tree)
+    int n = 0;
+    float lo[16][3], hi[16][3];
+    uint32_t child[16];
+};
+
 struct RayTrace {
     std::vector<uint8_t> runs;  // node visits before each leaf visit; the last run ends the ray
     bool last_has_leaf = false;
@@ -210,6 +216,8 @@ static SimtResult simt(const std::vector<const RayTrace*>& rays, size_t per_iter
     return R;
 }
 
+static double envd(const char* k, double d) { return getenv(k) ? atof(getenv(k)) : d; }
+
 int main(int argc, char** argv) {
     const char* name = argc > 1 ? argv[1] : "sphere_scene";
     int W = argc > 2 ? atoi(argv[2]) : 480, H = argc > 3 ? atoi(argv[3]) : 270, spp = argc > 4 ? atoi(argv[4]) : 4;
@@ -241,6 +249,61 @@ int main(int argc, char** argv) {
     printf("%s: %u world prims in the tree, %zu giants, %zu nodes, depth %u, sah %.3f\n", name, bvh.n_world_prims, giants.size(),
            bvh.nodes.size(), bvh.max_depth, bvh.sah_cost);
 
+    // width-W tree for the model: collapse the 4-wide tree (the interior child with the largest area is replaced by its
+    // children while the node has room); BVH_WIDTH=4 reproduces the builder's tree
+    const int width = getenv("BVH_WIDTH") ? atoi(getenv("BVH_WIDTH")) : 4;
+    std::vector<WNode> wn(bvh.nodes.size());
+    {
+        auto area = [](const float* lo, const float* hi) {
+            float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+            return 2 * (dx * dy + dy * dz + dz * dx);
+        };
+        for (size_t i = 0; i < bvh.nodes.size(); i++) {
+            const BvhNode4& b = bvh.nodes[i];
+            WNode& w = wn[i];
+            for (uint32_t k = 0; k < b.pad[0]; k++) {
+                w.lo[w.n][0] = b.lox[k]; w.lo[w.n][1] = b.loy[k]; w.lo[w.n][2] = b.loz[k];
+                w.hi[w.n][0] = b.hix[k]; w.hi[w.n][1] = b.hiy[k]; w.hi[w.n][2] = b.hiz[k];
+                w.child[w.n++] = b.child[k];
+            }
+        }
+        if (width > 4) {
+            // top-down so that a node's children are already-final 4-wide nodes when pulled up (use the original copies)
+            std::vector<WNode> orig = wn;
+            std::vector<uint32_t> todo{0};
+            size_t used = 0;
+            while (!todo.empty()) {
+                uint32_t id = todo.back();
+                todo.pop_back();
+                used++;
+                WNode w = orig[id];
+                for (;;) {
+                    int pick = -1;
+                    float best = -1;
+                    for (int k = 0; k < w.n; k++)
+                        if (!(w.child[k] & LEAF_FLAG)) {
+                            const WNode& ch = orig[w.child[k]];
+                            if (w.n - 1 + ch.n > width) continue;
+                            float a = area(w.lo[k], w.hi[k]);
+                            if (a > best) best = a, pick = k;
+                        }
+                    if (pick < 0) break;
+                    const WNode ch = orig[w.child[pick]];
+                    // replace slot `pick` with the first grandchild, append the rest
+                    for (int g = 0; g < ch.n; g++) {
+                        int slot = g == 0 ? pick : w.n++;
+                        memcpy(w.lo[slot], ch.lo[g], 12);
+                        memcpy(w.hi[slot], ch.hi[g], 12);
+                        w.child[slot] = ch.child[g];
+                    }
+                }
+                wn[id] = w;
+                for (int k = 0; k < w.n; k++)
+                    if (!(w.child[k] & LEAF_FLAG)) todo.push_back(w.child[k]);
+            }
+            printf("width %d: %zu nodes reachable\n", width, used);
+        }
+    }
     const RtCamera& cam = fs->camera;
     Counters cnt[2];  // camera rays, scattered rays
     unsigned long long hist_visits[64] = {0};
@@ -279,18 +342,16 @@ int main(int argc, char** argv) {
                     const uint32_t NONE = 0x7fffffffu;
                     while (cur != NONE) {
                         while (!(cur & LEAF_FLAG) && cur != NONE) {
-                            const BvhNode4& nd = bvh.nodes[cur];
+                            const WNode& nd = wn[cur];
                             c.visits++;
                             my_visits++;
                             run++;
-                            c.boxes += nd.pad[0];
-                            float e[4];
-                            const float* lo[3] = {nd.lox, nd.loy, nd.loz};
-                            const float* hi[3] = {nd.hix, nd.hiy, nd.hiz};
-                            for (int k = 0; k < 4; k++) {
+                            c.boxes += nd.n;
+                            float e[16];
+                            for (int k = 0; k < nd.n; k++) {
                                 float tn = 1e-3f, tf = best;
                                 for (int a = 0; a < 3; a++) {
-                                    float t0 = (lo[a][k] - oo[a]) * inv[a], t1 = (hi[a][k] - oo[a]) * inv[a];
+                                    float t0 = (nd.lo[k][a] - oo[a]) * inv[a], t1 = (nd.hi[k][a] - oo[a]) * inv[a];
                                     if (inv[a] < 0) std::swap(t0, t1);
                                     tn = std::fmax(tn, t0);
                                     tf = std::fmin(tf, t1);
@@ -298,10 +359,10 @@ int main(int argc, char** argv) {
                                 e[k] = tn <= tf ? tn : INFINITY;
                             }
                             int nk = 0;
-                            for (int k = 1; k < 4; k++)
+                            for (int k = 1; k < nd.n; k++)
                                 if (e[k] < e[nk]) nk = k;
                             if (e[nk] < INFINITY) {
-                                for (int k = 0; k < 4; k++)
+                                for (int k = 0; k < nd.n; k++)
                                     if (k != nk && e[k] < INFINITY) stack[sp++] = {nd.child[k], e[k]}, c.pushes++;
                                 cur = nd.child[nk];
                             } else {
@@ -388,6 +449,7 @@ int main(int argc, char** argv) {
            (double)(cnt[0].visits + cnt[1].visits) / R, (double)(cnt[0].boxes + cnt[1].boxes) / R, (double)(cnt[0].prims + cnt[1].prims) / R,
            (double)R / cnt[0].rays);
     // SIMT model of the scattered-ray traversal (argv[5] = scattered rays per block iteration)
+    const double CN = envd("COST_NODE", 118), CL = envd("COST_LEAF", 70), CF = envd("COST_FETCH", 150);
     {
         std::vector<const RayTrace*> sc;
         // the shade phase emits scattered rays class by class; approximate by path order within chunks of the pool
@@ -404,17 +466,17 @@ int main(int argc, char** argv) {
         for (int thr : {1, 4, 8, 16, 24, 32}) {
             char nm[64];
             snprintf(nm, sizeof nm, "while-while thr %d", thr);
-            show(nm, simt(sc, per_iter, 12, thr, 0, 118, 70, 150));
+            show(nm, simt(sc, per_iter, 12, thr, 0, CN, CL, CF));
         }
         for (int k : {1, 2, 3}) {
             char nm[64];
             snprintf(nm, sizeof nm, "if-if k=%d thr 8", k);
-            show(nm, simt(sc, per_iter, 12, 8, k, 118, 70, 150));
+            show(nm, simt(sc, per_iter, 12, 8, k, CN, CL, CF));
         }
         for (size_t n : {335, 670, 1340, 2680, 100000}) {
             char nm[64];
             snprintf(nm, sizeof nm, "thr 8, %zu rays/iter", n);
-            show(nm, simt(sc, n, 12, 8, 0, 118, 70, 150));
+            show(nm, simt(sc, n, 12, 8, 0, CN, CL, CF));
         }
     }
     // both parts of the todo list: per iteration `per_iter` scattered rays followed by the camera rays that replace ended paths
@@ -435,13 +497,13 @@ int main(int argc, char** argv) {
             printf("%-28s %10.2f %10.2f %10.2f %9.1f%% %9.1f%% %10.2f %10.3f\n", nm, r.node_lane_visits / r.node_steps, r.leaf_lane_visits / r.leaf_steps,
                    r.fetch_lanes / r.fetch_steps, 100 * r.idle_done / slots, 100 * r.idle_leaf / slots, r.issue / mix.size(), r.phase / mix.size());
         };
-        show("A2 refill, then A1 coherent", simt(mix, n_sc + n_cam, 12, 8, 0, 118, 70, 150, n_cam, 0));
-        show("one list, refill throughout", simt(mix, n_sc + n_cam, 12, 8, 0, 118, 70, 150, n_cam, 1));
-        show("one list, thr 16", simt(mix, n_sc + n_cam, 12, 16, 0, 118, 70, 150, n_cam, 1));
-        show("one list, thr 24", simt(mix, n_sc + n_cam, 12, 24, 0, 118, 70, 150, n_cam, 1));
-        show("one list, mid-round refill 8", simt(mix, n_sc + n_cam, 12, 8, 0, 118, 70, 150, n_cam, 1, 8));
-        show("one list, mid-round refill 16", simt(mix, n_sc + n_cam, 12, 16, 0, 118, 70, 150, n_cam, 1, 16));
-        show("one list, mid-round refill 4", simt(mix, n_sc + n_cam, 12, 4, 0, 118, 70, 150, n_cam, 1, 4));
+        show("A2 refill, then A1 coherent", simt(mix, n_sc + n_cam, 12, 8, 0, CN, CL, CF, n_cam, 0));
+        show("one list, refill throughout", simt(mix, n_sc + n_cam, 12, 8, 0, CN, CL, CF, n_cam, 1));
+        show("one list, thr 16", simt(mix, n_sc + n_cam, 12, 16, 0, CN, CL, CF, n_cam, 1));
+        show("one list, thr 24", simt(mix, n_sc + n_cam, 12, 24, 0, CN, CL, CF, n_cam, 1));
+        show("one list, mid-round refill 8", simt(mix, n_sc + n_cam, 12, 8, 0, CN, CL, CF, n_cam, 1, 8));
+        show("one list, mid-round refill 16", simt(mix, n_sc + n_cam, 12, 16, 0, CN, CL, CF, n_cam, 1, 16));
+        show("one list, mid-round refill 4", simt(mix, n_sc + n_cam, 12, 4, 0, CN, CL, CF, n_cam, 1, 4));
     }
     rt_host_scene_destroy(hs);
     return 0;
