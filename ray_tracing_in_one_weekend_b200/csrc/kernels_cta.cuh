@@ -1,8 +1,9 @@
 // CTA-local wavefront renderer (sm_100a): the whole wavefront loop runs INSIDE one persistent kernel.
 //
-// Every thread block (384 threads — 320 for the media feature sets — two blocks per SM) owns a pool of N = 1152 paths in shared memory (64 B of
-// path state + 18 B of queue space per path = 92 KB per block out of Blackwell's 227 KB per SM) and iterates,
-// separated by __syncthreads():
+// Every thread block (384 threads — 320 for the media feature sets — two blocks per SM) owns a pool of N paths in shared
+// memory (N = 1152, or 1120 in the builds that may stage a Perlin table beside it: a compile-time constant of each build,
+// RT_CTA_POOL_PATHS; 64 B of path state + 18 B of queue space per path = 92 KB per block out of Blackwell's 227 KB per SM)
+// and iterates, separated by __syncthreads():
 //
 //   D  regenerate   one 64-bit atomicAdd per block and iteration reserves path indices for every path that
 //                   ended; threads generate the new camera rays (main.rs:88-93) into the dead slots and append
@@ -11,6 +12,8 @@
 //                   per lane, while-while BVH traversal (rt_device.cuh); idle lanes are refilled from the
 //                   counter as soon as `refill_idle` lanes of the warp are idle.  A1: then the camera rays, a
 //                   coherent warp of 32 at a time, run to completion (uniform chunks that fill the tail).
+//                   Small trees without media (CtaArgs.unified_todo): the refill runs on through the camera rays, so
+//                   the lanes a warp has left when the scattered part runs dry are topped up instead of finishing alone.
 //                   A lane that finishes writes (t, prim) back and appends the path to one of the block's seven
 //                   SHADE QUEUES in shared memory: queue 0 for a miss, else bits 9..11 of the primitive record.
 //                   The host assigns the queues per scene (rtgpu.cu assign_shade_queues): one per shading class
