@@ -211,6 +211,7 @@ def load_test_library() -> C.CDLL:
     lib.rt_test_medium_cases.argtypes = [vp, u32, vp, vp, vp, u32, vp]
     lib.rt_test_closest_hit_xi.argtypes = [vp, vp, vp, vp, u32, C.c_float, C.c_float, vp]
     lib.rt_test_bvh_validate.argtypes = [C.POINTER(RtFlatScene), u32, C.POINTER(RtBvhInfo)]
+    lib.rt_test_div3_sweep.argtypes = [vp, u32, u32, u32, C.POINTER(C.c_uint64)]
     _test_lib = lib
     return lib
 

@@ -228,6 +228,40 @@ RT_TEST_API int rt_test_closest_hit_xi(RtScene* s, const float* o, const float* 
     return RT_OK;
 }
 
+// operator/(V3f, float) (rt_device.cuh: three quotients through one refined reciprocal) against the IEEE division, for
+// EVERY mantissa of the divisor at one exponent: thread m divides every consecutive triple of `a_vals` by
+// s = +-(1.m) * 2^(exp_s - 127) both ways and counts the components whose bits differ.
+__global__ void k_div3_sweep(const float* __restrict__ a_vals, uint32_t n_a, uint32_t exp_s, uint32_t negate, unsigned long long* mism) {
+    const uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= (1u << 23)) return;
+    const float s = __uint_as_float((negate ? 0x80000000u : 0u) | (exp_s << 23) | m);
+    uint32_t bad = 0;
+    for (uint32_t i = 0; i + 2 < n_a; i++) {
+        const V3f a = mk3(a_vals[i], a_vals[i + 1], a_vals[i + 2]);
+        const V3f q = a / s;
+        bad += __float_as_uint(q.x) != __float_as_uint(__fdiv_rn(a.x, s));
+        bad += __float_as_uint(q.y) != __float_as_uint(__fdiv_rn(a.y, s));
+        bad += __float_as_uint(q.z) != __float_as_uint(__fdiv_rn(a.z, s));
+    }
+    if (bad) atomicAdd(mism, (unsigned long long)bad);
+}
+
+RT_TEST_API int rt_test_div3_sweep(const float* a_vals, uint32_t n_a, uint32_t exp_s, uint32_t negate, unsigned long long* out_mismatches) {
+    if (!a_vals || n_a < 3 || n_a > 4096 || exp_s < 1 || exp_s > 254 || !out_mismatches) return rt_fail(RT_ERR_ARG, "rt_test_div3_sweep: bad argument");
+    float* d_a = nullptr;
+    unsigned long long* d_m = nullptr;
+    CU_TRY(cudaMalloc(&d_a, n_a * sizeof(float)));
+    CU_TRY(cudaMalloc(&d_m, sizeof(unsigned long long)));
+    CU_TRY(cudaMemcpy(d_a, a_vals, n_a * sizeof(float), cudaMemcpyHostToDevice));
+    CU_TRY(cudaMemset(d_m, 0, sizeof(unsigned long long)));
+    k_div3_sweep<<<(1u << 23) / 256, 256>>>(d_a, n_a, exp_s, negate, d_m);
+    CU_TRY(cudaGetLastError());
+    CU_TRY(cudaMemcpy(out_mismatches, d_m, sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    cudaFree(d_a);
+    cudaFree(d_m);
+    return RT_OK;
+}
+
 // Host-only (no GPU): build the BVH of a flat scene and check its structural invariants —
 // every world primitive is referenced by exactly one leaf, child counts/encodings are sane, and
 // every child box encloses the boxes/leaves below it.  Returns 0 when valid.

@@ -126,3 +126,28 @@ def test_textures_and_sky_match_oracle(rtlib, oracle, scene_name):
     else:
         np.testing.assert_allclose(out, want, rtol=1e-6, atol=1e-7)
     scene.close()
+
+
+def test_div3_is_the_ieee_quotient(rtlib):
+    """`V3f / float` (rt_device.cuh: the three quotients of a normalize through ONE refined reciprocal) equals the IEEE
+    division bit for bit: every one of the 2^23 divisor mantissas at several exponents and both signs, against
+    numerators that cover the exponent range of the fast path and beyond it (zero, denormal, huge, inf, NaN take the
+    plain divisions), with adversarial mantissas (all ones, all zeros, one bit)."""
+    rt = rtlib
+    lib = rt.load_test_library()
+    rng = np.random.default_rng(7)
+    mant = np.array([0x000000, 0x7FFFFF, 0x7FFFFE, 0x000001, 0x400000, 0x3FFFFF, 0x555555, 0x2AAAAA], np.uint32)
+    vals = []
+    for e in (60, 67, 100, 126, 127, 128, 150, 187, 188):   # 2^-67 .. 2^61: both sides of the fast path's range
+        vals.append(((np.uint32(e) << np.uint32(23)) | mant).view(np.float32))
+    vals.append(rng.standard_normal(64).astype(np.float32))
+    vals.append((rng.random(32, dtype=np.float32) * 2 - 1) * np.float32(1e-3))
+    vals.append(np.array([0.0, -0.0, 1e-40, -1e-42, np.inf, -np.inf, np.nan, 3.0e38, 1.0, -1.0, 0.5, 1.5], np.float32))
+    a = np.concatenate(vals).astype(np.float32)
+    a[1::2] *= np.float32(-1)   # both signs
+    a = np.ascontiguousarray(a)
+    for exp_s, neg in ((127, 0), (126, 1), (100, 0), (150, 1), (66, 0), (188, 0), (30, 0), (230, 1)):
+        m = C.c_uint64(123)
+        rc = lib.rt_test_div3_sweep(a.ctypes.data, a.size, exp_s, neg, C.byref(m))
+        assert rc == 0, lib.rt_last_error()
+        assert m.value == 0, f"divisor exponent {exp_s - 127}, negate {neg}: {m.value} quotient components differ from IEEE division"

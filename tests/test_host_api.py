@@ -34,7 +34,7 @@ def test_library_exports_exactly_the_header(rtlib):
     # the test library = the same ABI plus the hooks, nothing else
     extra = _dynamic_symbols(rtlib.api.TEST_LIB_PATH) - declared
     assert extra == {"rt_test_shade_cases", "rt_test_texture_cases", "rt_test_medium_cases", "rt_test_closest_hit_xi",
-                     "rt_test_bvh_validate"}, extra
+                     "rt_test_bvh_validate", "rt_test_div3_sweep"}, extra
 
 
 def test_library_reads_no_environment(rtlib):
