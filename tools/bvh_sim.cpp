@@ -448,6 +448,16 @@ int main(int argc, char** argv) {
     printf("all       rays %10llu  visits/ray %6.3f  boxes/ray %6.2f  prims/ray %5.3f  rays/path %.3f\n", R,
            (double)(cnt[0].visits + cnt[1].visits) / R, (double)(cnt[0].boxes + cnt[1].boxes) / R, (double)(cnt[0].prims + cnt[1].prims) / R,
            (double)R / cnt[0].rays);
+    {
+        unsigned long long segs = 0, zero = 0, later = 0;
+        for (auto& t : traces)
+            for (size_t i = 0; i < t.runs.size(); i++) {
+                segs++;
+                if (i > 0) later++;
+                if (t.runs[i] == 0) zero++;
+            }
+        printf("segments %llu, after a leaf %llu, zero-length runs (a popped entry that is a leaf) %llu\n", segs, later, zero);
+    }
     // SIMT model of the scattered-ray traversal (argv[5] = scattered rays per block iteration)
     const double CN = envd("COST_NODE", 118), CL = envd("COST_LEAF", 70), CF = envd("COST_FETCH", 150);
     {
