@@ -1,3 +1,4 @@
+# Run on the GPU box with a run-time pool size variant (tools/build_variant.py rtp -DRT_CTA_POOL_PATHS=0): pool size / carve-out per scene.
 for c in "cover_100k_motion 1920 1080 32" "final_scene 1024 1024 64"; do
   for pc in "1120 -1" "928 -1" "736 -1" "736 60" "544 -1" "1120 100"; do
     set -- $c; a=($pc)
