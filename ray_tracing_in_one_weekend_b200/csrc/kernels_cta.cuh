@@ -1,6 +1,6 @@
 // CTA-local wavefront renderer (sm_100a): the whole wavefront loop runs INSIDE one persistent kernel.
 //
-// Every thread block (384 threads — 320 for the media feature sets — two blocks per SM) owns a pool of N paths in shared
+// Every thread block (448 threads for the sphere-only feature sets, 320 for the media sets, 384 otherwise; two blocks per SM) owns a pool of N paths in shared
 // memory (N = 1152, or 1120 in the builds that may stage a Perlin table beside it: a compile-time constant of each build,
 // RT_CTA_POOL_PATHS; 64 B of path state + 18 B of queue space per path = 92 KB per block out of Blackwell's 227 KB per SM)
 // and iterates, separated by __syncthreads():
@@ -48,9 +48,16 @@ namespace rtb {
 #if !defined(RT_CTA_THREADS) && defined(RT_CTA_FLAT_THREADS) && RT_CTA_FLAT
 #define RT_CTA_THREADS RT_CTA_FLAT_THREADS  // (development: block size of the tiny-scene builds only)
 #endif
+// Round 2, after the kernel lost 5 % of its instructions: the sphere-only sets (with or without motion) without the pbr.rs
+// class take 448 threads
+// (72 registers, 56 B of spills, 28 warps per SM) — cover scene +1.9 %, cover_4k_motion +1.4 %, cover_100k_motion
+// +1.5 %, textured +0.6 %; 512 threads (64 registers, 240 B of spills) lose 2-7 %, and 448 costs the flat builds 1-2 % and
+// the media set 15 % (profiles/r02_experiments/threads_448_sphere_sets.log).
 #ifndef RT_CTA_THREADS
 #if defined(RT_CTA_F) && ((RT_CTA_F) & 2) && !RT_CTA_FLAT
 #define RT_CTA_THREADS 320
+#elif defined(RT_CTA_F) && ((RT_CTA_F) & ~4) == 0 && !RT_CTA_FLAT && defined(RT_CTA_CLS_MASK) && (RT_CTA_CLS_MASK) == 0x3f
+#define RT_CTA_THREADS 448  // (the builds without the pbr.rs class: with it the 72-register build spills 100-180 B, unmeasured)
 #else
 #define RT_CTA_THREADS 384
 #endif
