@@ -33,3 +33,51 @@ def test_bvh_sim_builds_and_reports_tree_quality(tmp_path, rtlib):
     uni = re.search(r"^one list, refill throughout\s+[\d.]+\s+[\d.]+\s+[\d.]+\s+[\d.]+%\s+[\d.]+%\s+([\d.]+)", out, re.M)
     assert sep and uni, out[-1500:]
     assert float(uni.group(1)) < float(sep.group(1))
+
+
+def _res_usage(obj, kernel_substr):
+    out = subprocess.run(["cuobjdump", "-res-usage", os.path.join(PKG, "csrc", obj)], capture_output=True, text=True).stdout
+    lines = out.splitlines()
+    for i, l in enumerate(lines):
+        if "Function" in l and kernel_substr in l:
+            return {k: int(v) for k, v in re.findall(r"(REG|STACK|SHARED):(\d+)", lines[i + 1])}
+    raise AssertionError(f"{kernel_substr} not found in {obj}")
+
+
+def _sass(obj, kernel_substr):
+    out = subprocess.run(["cuobjdump", "-sass", os.path.join(PKG, "csrc", obj)], capture_output=True, text=True).stdout
+    keep, on = [], False
+    for l in out.splitlines():
+        if "Function :" in l:
+            on = kernel_substr in l
+        elif on and re.match(r"\s+/\*[0-9a-f]{4,5}\*/", l):
+            keep.append(l)
+    assert keep, f"{kernel_substr} not found in {obj}"
+    return keep
+
+
+def test_render_kernels_keep_their_register_budgets(rtlib):
+    """The block shapes in kernels_cta.cuh are chosen for these register counts (two blocks per SM): 448 threads x 72
+    registers for the sphere-only builds without the pbr.rs class, 384 x 80 for the others and the flat builds,
+    320 x 96 for the media sets.  A build that needs more would silently drop to one block per SM."""
+    for obj, kern, regs, stack in (("cta_f0_m3f.o", "ILj0ELb0ELj63ELb0E", 72, 640), ("cta_f4_m3f.o", "ILj4ELb0ELj63ELb0E", 72, 640),
+                                   ("cta_f0.o", "ILj0ELb0ELj127ELb0E", 80, 640), ("cta_f0_flat.o", "ILj0ELb0ELj127ELb1E", 80, 128),
+                                   ("cta_f11_flat.o", "ILj11ELb0ELj127ELb1E", 80, 128), ("cta_f11.o", "ILj11ELb0ELj127ELb0E", 96, 640),
+                                   ("cta_f15.o", "ILj15ELb0ELj127ELb0E", 96, 640)):
+        u = _res_usage(obj, kern)
+        assert u["REG"] <= regs and u["STACK"] <= stack, (obj, u)
+
+
+def test_headline_kernel_codegen(rtlib):
+    """SASS properties DESIGN.md section 5 relies on, for the headline instantiation (spheres only, no pbr.rs class):
+    three-input min/max in the slab tests, 128-bit node loads through the read-only path, and one-lane counter takes
+    that stay ONE shared-memory atomic (ptxas expands a provably warp-uniform address into a 17-instruction
+    vote / popcount / shuffle sequence: kernels_cta.cuh warp_take)."""
+    sass = _sass("cta_f0_m3f.o", "ILj0ELb0ELj63ELb0E")
+    n = lambda pat: sum(1 for l in sass if re.search(pat, l))
+    assert 7000 < len(sass) < 9000, len(sass)
+    assert n(r"FMNMX3") >= 16 and n(r"LDG\.E\.128\.CONSTANT") >= 14
+    assert n(r"ATOMS") >= 9
+    # aggregation sequences left: the per-lane appends to the todo / dead lists (wanted there), none for the takes
+    assert n(r"VOTEU\.ANY") <= 12, n(r"VOTEU\.ANY")
+    assert n(r"\bHMMA|\bWGMMA|UTCMMA") == 0   # nothing on this path is a dense contraction (DESIGN.md section 5)
